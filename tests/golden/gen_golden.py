@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""Generate golden input/output vectors by running the UNMODIFIED reference on CPU.
+
+Run in the build container only (``/root/reference`` does not exist on the GPU
+box); the ``.npz`` files it writes next to itself are committed and are what the
+tests read.  Usage::
+
+    python tests/golden/gen_golden.py
+
+The reference needs: a ``colorama`` stand-in (its only missing dependency),
+``flash_attn`` hidden so that ``Attention.forward`` takes the eager branch
+(attention.py:80-87,450-453), and ``MINIVLLM_DEVICE=cpu``.
+
+Every case is seeded (``torch.Generator().manual_seed``).  bf16 tensors are
+stored as uint16 bit patterns.  What is recorded:
+
+* ``store_*``   : ``StandardAttentionBackend.store_kv_cache`` (attention_backend.py:196-266)
+* ``decode_*``  : ``PageAttention.__call__`` (page_attention.py:35-133); the five
+                  fp32 shapes are the reference's own tests/test_page_attention.py:95-276
+* ``prefill_*`` : ``Attention._fallback_attention`` prefill branch (attention.py:467-504)
+* ``layer_*``   : ``Attention.forward`` prefill then decode steps through the
+                  real ``Context`` (attention.py:196-455), caches included
+"""
+
+from __future__ import annotations
+
+import os
+import sys
+import tempfile
+import types
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REFERENCE = os.environ.get("MINIVLLM_REFERENCE", "/root/reference")
+
+
+def _import_reference():
+    os.environ.setdefault("MINIVLLM_DEVICE", "cpu")
+    os.environ["CUDA_VISIBLE_DEVICES"] = ""
+    shim = types.ModuleType("colorama")
+
+    class _Blank:
+        def __getattr__(self, _name):
+            return ""
+
+    shim.Fore = shim.Style = shim.Back = _Blank()
+    shim.init = lambda *a, **k: None
+    sys.modules.setdefault("colorama", shim)
+    sys.modules["flash_attn"] = None  # force the eager branch
+    sys.path.insert(0, REFERENCE)
+    import minivllm  # noqa: F401
+
+
+_import_reference()
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+from minivllm.models.layers.attention import Attention  # noqa: E402
+from minivllm.models.layers.attention_backend import StandardAttentionBackend  # noqa: E402
+from minivllm.models.layers.page_attention import PageAttention  # noqa: E402
+from minivllm.utils.context import reset_context, set_context  # noqa: E402
+
+torch.set_num_threads(4)
+
+
+def to_np(t: torch.Tensor) -> np.ndarray:
+    t = t.detach().contiguous()
+    if t.dtype == torch.bfloat16:
+        return t.view(torch.int16).numpy().view(np.uint16).copy()
+    if t.dtype == torch.float16:
+        return t.view(torch.int16).numpy().view(np.float16).copy()
+    return t.numpy().copy()
+
+
+def randn(gen, *shape, dtype=torch.float32):
+    return torch.randn(*shape, generator=gen, dtype=torch.float32).to(dtype)
+
+
+def dtype_name(dt):
+    return {torch.float32: "f32", torch.bfloat16: "bf16", torch.float16: "f16"}[dt]
+
+
+def save(name, **arrays):
+    path = os.path.join(HERE, name + ".npz")
+    np.savez_compressed(path, **arrays)
+    print(f"  wrote {name}.npz  ({os.path.getsize(path) / 1024:.0f} KiB)")
+
+
+# ---------------------------------------------------------------------------
+# store
+# ---------------------------------------------------------------------------
+
+
+def gen_store():
+    backend = StandardAttentionBackend()
+    out = {}
+    cases = [
+        # name, N, KVH, D, num_slots, dtype, slots-kind, strided
+        ("ref_basic", 2, 4, 16, 100, torch.float32, [10, 20], False),
+        ("ref_noncontig", 3, 4, 16, 50, torch.float32, [0, 25, 49], False),
+        ("bf16_prefill", 150, 2, 128, 256, torch.bfloat16, "prefill", True),
+        ("bf16_decode_pad", 16, 8, 128, 96, torch.bfloat16, "decode_pad", True),
+        ("f16_opt", 37, 12, 64, 128, torch.float16, "perm", False),
+        ("f32_odd", 9, 3, 20, 64, torch.float32, "perm", True),
+    ]
+    for idx, (name, n, kvh, d, slots_n, dt, kind, strided) in enumerate(cases):
+        g = torch.Generator().manual_seed(100 + idx)
+        if strided:
+            # k and v as row-strided views of one fused projection output
+            fused = randn(g, n, 3 * kvh * d + 8, dtype=dt)
+            key = fused[:, kvh * d : 2 * kvh * d].view(n, kvh, d)
+            value = fused[:, 2 * kvh * d : 3 * kvh * d].view(n, kvh, d)
+        else:
+            key = randn(g, n, kvh, d, dtype=dt)
+            value = randn(g, n, kvh, d, dtype=dt)
+        if isinstance(kind, list):
+            slots = torch.tensor(kind, dtype=torch.int64)
+        elif kind == "prefill":
+            # blocks 3,1,2 of 64 slots, last partial: 64+64+22 = 150 tokens
+            slots = torch.tensor(
+                list(range(192, 256)) + list(range(64, 128)) + list(range(128, 150)),
+                dtype=torch.int32,
+            )
+        elif kind == "decode_pad":
+            perm = torch.randperm(slots_n, generator=g)[:n].to(torch.int32)
+            perm[n - 5 :] = -1  # graph padding rows
+            perm[2] = -1
+            slots = perm
+        else:
+            slots = torch.randperm(slots_n, generator=g)[:n].to(torch.int32)
+        k_cache = randn(g, slots_n, kvh * d, dtype=dt)
+        v_cache = randn(g, slots_n, kvh * d, dtype=dt)
+        out[f"{name}.key"] = to_np(key)
+        out[f"{name}.value"] = to_np(value)
+        out[f"{name}.slots"] = to_np(slots)
+        out[f"{name}.k_cache_in"] = to_np(k_cache)
+        out[f"{name}.v_cache_in"] = to_np(v_cache)
+        backend.store_kv_cache(key, value, k_cache, v_cache, slots)
+        out[f"{name}.k_cache_out"] = to_np(k_cache)
+        out[f"{name}.v_cache_out"] = to_np(v_cache)
+        out[f"{name}.meta"] = np.array([n, kvh, d, slots_n, int(strided)])
+        out[f"{name}.dtype"] = np.array(dtype_name(dt))
+    out["cases"] = np.array([c[0] for c in cases])
+    save("store", **out)
+
+
+# ---------------------------------------------------------------------------
+# decode
+# ---------------------------------------------------------------------------
+
+
+def build_paged(g, seqlens, block_tables, bs, kvh, d, dt, num_blocks=None):
+    """Scatter per-sequence contiguous K/V into a paged cache (garbage elsewhere)."""
+    bt = torch.tensor(block_tables, dtype=torch.int32)
+    nb = num_blocks or int(bt.max().item()) + 1
+    # unwritten slots hold finite garbage so that masking mistakes show up
+    k_cache = randn(g, nb, bs, kvh, d, dtype=dt) * 3
+    v_cache = randn(g, nb, bs, kvh, d, dtype=dt) * 3
+    for b, sl in enumerate(seqlens):
+        kk = randn(g, sl, kvh, d, dtype=dt)
+        vv = randn(g, sl, kvh, d, dtype=dt)
+        for p in range(sl):
+            blk = int(bt[b, p // bs])
+            k_cache[blk, p % bs] = kk[p]
+            v_cache[blk, p % bs] = vv[p]
+    return k_cache, v_cache, bt
+
+
+def gen_decode():
+    pa = PageAttention()
+    out = {}
+    cases = [
+        # name, H, KVH, D, BS, seqlens, block_tables, dtype
+        ("ref_single_block", 8, 8, 64, 16, [12], [[0]], torch.float32),
+        ("ref_multi_block", 8, 8, 64, 4, [10], [[5, 2, 7]], torch.float32),
+        ("ref_multi_seq", 8, 8, 64, 8, [15, 8, 20], [[3, 1, 0], [2, -1, -1], [5, 4, 6]], torch.float32),
+        ("ref_gqa", 8, 2, 64, 8, [16, 10], [[0, 1], [2, 3]], torch.float32),
+        ("ref_varying", 4, 4, 32, 4, [4, 7, 3], [[0, 1], [2, 3], [4, -1]], torch.float32),
+        # engine-shaped: BS=64, D=128 (Qwen) / 64 (OPT), bf16
+        ("qwen3_g2", 4, 2, 128, 64, [1, 63, 64, 65, 300], None, torch.bfloat16),
+        ("qwen3_g4", 8, 2, 128, 64, [200, 129, 5], None, torch.bfloat16),
+        ("qwen2_g7", 7, 1, 128, 64, [257, 64, 33], None, torch.bfloat16),
+        ("qwen2_g8", 8, 1, 128, 64, [513, 100], None, torch.bfloat16),
+        ("opt_mha", 4, 4, 64, 64, [70, 3, 128], None, torch.float16),
+        ("opt_mha_f32", 4, 4, 64, 64, [70, 3, 128], None, torch.float32),
+    ]
+    for idx, (name, h, kvh, d, bs, seqlens, bt, dt) in enumerate(cases):
+        g = torch.Generator().manual_seed(200 + idx)
+        if bt is None:
+            # non-contiguous physical pages, -1 padded like _prepare_block_tables
+            nblk = [(s + bs - 1) // bs for s in seqlens]
+            total = sum(nblk) + 3
+            perm = torch.randperm(total, generator=g).tolist()
+            width = max(nblk)
+            bt, c = [], 0
+            for nb in nblk:
+                bt.append(perm[c : c + nb] + [-1] * (width - nb))
+                c += nb
+            num_blocks = total
+        else:
+            num_blocks = None
+        k_cache, v_cache, btt = build_paged(g, seqlens, bt, bs, kvh, d, dt, num_blocks)
+        q = randn(g, len(seqlens), h, d, dtype=dt)
+        ctx = torch.tensor(seqlens, dtype=torch.int32)
+        scale = 1.0 / (d**0.5)
+        ref = pa(q, k_cache, v_cache, btt, ctx, scale)
+        out[f"{name}.q"] = to_np(q)
+        out[f"{name}.k_cache"] = to_np(k_cache)
+        out[f"{name}.v_cache"] = to_np(v_cache)
+        out[f"{name}.block_tables"] = to_np(btt)
+        out[f"{name}.context_lens"] = to_np(ctx)
+        out[f"{name}.out"] = to_np(ref)
+        out[f"{name}.scale"] = np.array(scale)
+        out[f"{name}.dtype"] = np.array(dtype_name(dt))
+    out["cases"] = np.array([c[0] for c in cases])
+    save("decode", **out)
+
+
+# ---------------------------------------------------------------------------
+# dense prefill (no prefix hits): Attention._fallback_attention
+# ---------------------------------------------------------------------------
+
+
+def gen_prefill():
+    out = {}
+    cases = [
+        ("f32_gqa4", 8, 2, 64, [5, 17, 1], torch.float32),
+        ("f32_mha", 4, 4, 32, [33, 2], torch.float32),
+        ("bf16_qwen3", 4, 2, 128, [130, 64, 257, 1], torch.bfloat16),
+        ("bf16_g7", 7, 1, 128, [129, 200], torch.bfloat16),
+        ("f16_opt", 4, 4, 64, [100, 31], torch.float16),
+    ]
+    for idx, (name, h, kvh, d, seqlens, dt) in enumerate(cases):
+        g = torch.Generator().manual_seed(300 + idx)
+        n = sum(seqlens)
+        q = randn(g, n, h, d, dtype=dt)
+        k = randn(g, n, kvh, d, dtype=dt)
+        v = randn(g, n, kvh, d, dtype=dt)
+        cu = torch.tensor([0] + list(np.cumsum(seqlens)), dtype=torch.int32)
+        scale = 1.0 / (d**0.5)
+        attn = Attention(h, d, scale, kvh)
+        set_context(
+            is_prefill=True,
+            max_seqlen_q=max(seqlens),
+            max_seqlen_k=max(seqlens),
+            cum_seqlens_q=cu,
+            cum_seqlens_k=cu,
+        )
+        try:
+            with torch.no_grad():
+                ref = attn(q, k, v)  # caches empty -> no store; eager prefill
+        finally:
+            reset_context()
+        out[f"{name}.q"] = to_np(q)
+        out[f"{name}.k"] = to_np(k)
+        out[f"{name}.v"] = to_np(v)
+        out[f"{name}.cu_seqlens"] = to_np(cu)
+        out[f"{name}.out"] = to_np(ref)
+        out[f"{name}.scale"] = np.array(scale)
+        out[f"{name}.dtype"] = np.array(dtype_name(dt))
+    out["cases"] = np.array([c[0] for c in cases])
+    save("prefill", **out)
+
+
+# ---------------------------------------------------------------------------
+# whole layer: prefill (store + attention) then decode steps through Context
+# ---------------------------------------------------------------------------
+
+
+def gen_layer():
+    out = {}
+    cases = [
+        ("bf16_qwen3", 4, 2, 128, [70, 130, 64], 3, torch.bfloat16),
+        ("f32_opt", 4, 4, 64, [20, 65], 2, torch.float32),
+    ]
+    bs = 64
+    for idx, (name, h, kvh, d, seqlens, steps, dt) in enumerate(cases):
+        g = torch.Generator().manual_seed(400 + idx)
+        scale = 1.0 / (d**0.5)
+        attn = Attention(h, d, scale, kvh)
+        final = [s + steps for s in seqlens]
+        nblk = [(s + bs - 1) // bs for s in final]
+        total = sum(nblk) + 2
+        perm = torch.randperm(total, generator=g).tolist()
+        tables, c = [], 0
+        for nb in nblk:
+            tables.append(perm[c : c + nb])
+            c += nb
+        attn.k_cache = randn(g, total, bs, kvh, d, dtype=dt) * 2
+        attn.v_cache = randn(g, total, bs, kvh, d, dtype=dt) * 2
+        out[f"{name}.k_cache_in"] = to_np(attn.k_cache)
+        out[f"{name}.v_cache_in"] = to_np(attn.v_cache)
+        # ---- prefill
+        n = sum(seqlens)
+        q = randn(g, n, h, d, dtype=dt)
+        k = randn(g, n, kvh, d, dtype=dt)
+        v = randn(g, n, kvh, d, dtype=dt)
+        cu = torch.tensor([0] + list(np.cumsum(seqlens)), dtype=torch.int32)
+        slots = []
+        for sl, tb in zip(seqlens, tables):
+            for p in range(sl):
+                slots.append(tb[p // bs] * bs + p % bs)
+        slots_t = torch.tensor(slots, dtype=torch.int32)
+        width = max((s + bs - 1) // bs for s in seqlens)
+        bt = torch.tensor(
+            [tb[: (s + bs - 1) // bs] + [-1] * (width - (s + bs - 1) // bs) for s, tb in zip(seqlens, tables)],
+            dtype=torch.int32,
+        )
+        set_context(
+            is_prefill=True,
+            max_seqlen_q=max(seqlens),
+            max_seqlen_k=max(seqlens),
+            cum_seqlens_q=cu,
+            cum_seqlens_k=cu,
+            slot_mapping=slots_t,
+            block_tables=bt,
+        )
+        try:
+            with torch.no_grad():
+                o = attn(q, k, v)
+        finally:
+            reset_context()
+        out[f"{name}.p.q"] = to_np(q)
+        out[f"{name}.p.k"] = to_np(k)
+        out[f"{name}.p.v"] = to_np(v)
+        out[f"{name}.p.cu_seqlens"] = to_np(cu)
+        out[f"{name}.p.slots"] = to_np(slots_t)
+        out[f"{name}.p.block_tables"] = to_np(bt)
+        out[f"{name}.p.out"] = to_np(o)
+        out[f"{name}.p.k_cache_out"] = to_np(attn.k_cache)
+        out[f"{name}.p.v_cache_out"] = to_np(attn.v_cache)
+        # ---- decode steps
+        lens = list(seqlens)
+        b = len(lens)
+        for st in range(steps):
+            lens = [x + 1 for x in lens]
+            q = randn(g, b, h, d, dtype=dt)
+            k = randn(g, b, kvh, d, dtype=dt)
+            v = randn(g, b, kvh, d, dtype=dt)
+            slots_t = torch.tensor(
+                [tb[(x - 1) // bs] * bs + (x - 1) % bs for x, tb in zip(lens, tables)],
+                dtype=torch.int32,
+            )
+            width = max((x + bs - 1) // bs for x in lens)
+            bt = torch.tensor(
+                [tb[: (x + bs - 1) // bs] + [-1] * (width - (x + bs - 1) // bs) for x, tb in zip(lens, tables)],
+                dtype=torch.int32,
+            )
+            ctx = torch.tensor(lens, dtype=torch.int32)
+            set_context(is_prefill=False, slot_mapping=slots_t, context_lens=ctx, block_tables=bt)
+            try:
+                with torch.no_grad():
+                    o = attn(q, k, v)
+            finally:
+                reset_context()
+            pre = f"{name}.d{st}"
+            out[f"{pre}.q"] = to_np(q)
+            out[f"{pre}.k"] = to_np(k)
+            out[f"{pre}.v"] = to_np(v)
+            out[f"{pre}.slots"] = to_np(slots_t)
+            out[f"{pre}.block_tables"] = to_np(bt)
+            out[f"{pre}.context_lens"] = to_np(ctx)
+            out[f"{pre}.out"] = to_np(o)
+        out[f"{name}.k_cache_final"] = to_np(attn.k_cache)
+        out[f"{name}.v_cache_final"] = to_np(attn.v_cache)
+        out[f"{name}.meta"] = np.array([h, kvh, d, steps, len(seqlens)])
+        out[f"{name}.scale"] = np.array(scale)
+        out[f"{name}.dtype"] = np.array(dtype_name(dt))
+    out["cases"] = np.array([c[0] for c in cases])
+    save("layer", **out)
+
+
+if __name__ == "__main__":
+    print("generating golden vectors from", REFERENCE)
+    gen_store()
+    gen_decode()
+    gen_prefill()
+    gen_layer()
