@@ -1,0 +1,388 @@
+#!/usr/bin/env python
+"""bench.py — the hot path on BASELINE.json's headline configuration.
+
+Workload (``configs[1]``): Qwen3-0.6B decode, 256 sequences x 2048-token context,
+bf16, CUDA Graph on.  One *step* = one decode step's attention hot path over the
+whole batch: for each of the 28 layers, ``store_kvcache`` of the 256 new K/V rows
+followed by paged split-KV GQA decode attention over that layer's own paged cache
+(62 GB of KV in HBM at N=1, so every step streams inputs far larger than L2).
+
+metric  = paged-attn decode KV-read GB/s (algorithmic K+V bytes of the batch / step time)
+value   = device-timed, inputs resident in HBM, the 28-layer step replayed as one CUDA graph
+e2e     = same metric through ``Attention.forward`` with HOST (pinned) q/k/v per layer:
+          H2D of inputs + metadata and D2H of every layer's output inside the timed region
+roofline= the dominant kernel (paged_decode_kernel) timed alone, against measured HBM peak
+N > 1   = the reference's tensor-parallel split: KV/Q heads shard over ranks, no collective
+          in the path (NCCL only for the barrier and the max-over-ranks of the time)
+
+``--impl reference`` times the reference's CPU eager path (oracle/eager_port.py, the torch-CPU
+port of page_attention.py / attention_backend.py) on a bounded sample of the same workload.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: layers, H, KVH, D, batch, ctx
+    "cfg2": dict(name="Qwen3-0.6B decode 256 seqs x 2048 ctx, bf16, CUDA Graph", layers=28, H=16, KVH=8, D=128, batch=256, ctx=2048),
+    "cfg4": dict(name="Qwen2-7B decode 1 seq x 32768 ctx (split-KV stress), bf16, CUDA Graph", layers=28, H=28, KVH=4, D=128, batch=1, ctx=32768),
+    "tiny": dict(name="debug", layers=2, H=16, KVH=8, D=128, batch=8, ctx=512),
+}
+BLOCK = 64
+METRIC = "paged-attn decode KV-read GB/s"
+
+
+def kv_bytes_per_layer(batch, ctx, kvh, d, elem=2):
+    """sum_b ctx_b * KVH * D * 2 (K and V) * elem."""
+    return batch * ctx * kvh * d * 2 * elem
+
+
+# ---------------------------------------------------------------------------
+# clocks sampler (nvidia-smi during the timed region)
+# ---------------------------------------------------------------------------
+
+
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                r = subprocess.run(
+                    ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits"],
+                    capture_output=True, text=True, timeout=5,
+                )
+                if r.returncode == 0 and r.stdout.strip():
+                    self.samples.append([x.strip() for x in r.stdout.strip().splitlines()[0].split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for s in self.samples:
+            try:
+                sm.append(float(s[0]))
+                mx = max(mx, float(s[1]))
+            except (ValueError, IndexError):
+                continue
+            for nm, val in zip(names, s[2:6]):
+                if val.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# reference arm / cpu_baseline: the torch-CPU eager port on a bounded sample
+# ---------------------------------------------------------------------------
+
+
+def cpu_sample_setup(wl, sample_batch, sample_layers, seed=0):
+    import torch
+
+    g = torch.Generator().manual_seed(seed)
+    kvh, h, d, ctx = wl["KVH"], wl["H"], wl["D"], wl["ctx"]
+    nblk = ctx // BLOCK + 1
+    nb = sample_batch * nblk
+    caches = []
+    for _ in range(sample_layers):
+        kc = torch.randn(nb, BLOCK, kvh, d, generator=g).to(torch.bfloat16)
+        vc = torch.randn(nb, BLOCK, kvh, d, generator=g).to(torch.bfloat16)
+        caches.append((kc, vc))
+    perm = torch.randperm(nb, generator=g).view(sample_batch, nblk).to(torch.int32)
+    ctx_lens = torch.full((sample_batch,), ctx, dtype=torch.int32)
+    slots = (perm[:, (ctx - 1) // BLOCK].long() * BLOCK + (ctx - 1) % BLOCK).to(torch.int32)
+    q = torch.randn(sample_batch, h, d, generator=g).to(torch.bfloat16)
+    k = torch.randn(sample_batch, kvh, d, generator=g).to(torch.bfloat16)
+    v = torch.randn(sample_batch, kvh, d, generator=g).to(torch.bfloat16)
+    return caches, perm, ctx_lens, slots, q, k, v
+
+
+def cpu_step(port, caches, perm, ctx_lens, slots, q, k, v, scale):
+    out = None
+    for kc, vc in caches:
+        port.store_kvcache(k, v, kc, vc, slots)
+        out = port.paged_decode(q, kc, vc, perm, ctx_lens, scale)
+    return out
+
+
+def run_cpu_baseline(wl, steps, warmup, sample_batch=32, sample_layers=4):
+    import torch
+
+    from oracle import eager_port as port
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    state = cpu_sample_setup(wl, sample_batch, sample_layers)
+    scale = wl["D"] ** -0.5
+    for _ in range(max(1, warmup)):
+        cpu_step(port, *state, scale)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_step(port, *state, scale)
+    dt = (time.perf_counter() - t0) / steps
+    nbytes = kv_bytes_per_layer(sample_batch, wl["ctx"], wl["KVH"], wl["D"]) * sample_layers
+    return {
+        "value": nbytes / dt / 1e9, "unit": "GB/s", "cores": torch.get_num_threads(), "kind": "port",
+        "sample": f"{sample_batch} of {wl['batch']} sequences x {wl['ctx']} ctx, {sample_layers} of {wl['layers']} layers, "
+                  f"bf16, store+paged decode per layer (oracle/eager_port.py = torch-CPU port of page_attention.py:35-133)",
+        "ms_per_step": dt * 1e3,
+    }
+
+
+def run_reference_arm(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    base = run_cpu_baseline(wl, args.steps, args.warmup)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": "GB/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": base["ms_per_step"], "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": wl["name"], "sample": base["sample"]},
+        "cpu_baseline": {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": base["value"], "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------
+# the B200 arm
+# ---------------------------------------------------------------------------
+
+
+def run_b200(args, wl):
+    import torch
+    import torch.distributed as dist
+
+    import minivllm_b200 as m
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback for the product path)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    tp = world
+    if wl["H"] % tp or wl["KVH"] % tp:
+        raise SystemExit(f"TP={tp} does not divide H={wl['H']} / KVH={wl['KVH']} (reference rule qwen_base.py:95-104)")
+    L, H, KVH, D = wl["layers"], wl["H"] // tp, wl["KVH"] // tp, wl["D"]
+    B, ctx = wl["batch"], wl["ctx"]
+    scale = D**-0.5
+    nblk = ctx // BLOCK + 1
+    NB = B * nblk
+    torch.manual_seed(1234 + rank)
+
+    # ---- paged cache [2, L, NB, 64, KVH/tp, D] (inference_executor.py:209-221), random contents
+    kv_cache = torch.empty(2, L, NB, BLOCK, KVH, D, dtype=torch.bfloat16, device=dev)
+    flat = kv_cache.view(-1)
+    chunk = 1 << 28
+    for i in range(0, flat.numel(), chunk):
+        flat[i : i + chunk].normal_()
+    g = torch.Generator().manual_seed(0)
+    block_tables = torch.randperm(NB, generator=g).view(B, nblk).to(torch.int32).to(dev)  # non-contiguous pages
+    context_lens = torch.full((B,), ctx, dtype=torch.int32, device=dev)
+    slot_mapping = (block_tables[:, (ctx - 1) // BLOCK].long() * BLOCK + (ctx - 1) % BLOCK).to(torch.int32)
+
+    layers = []
+    for l in range(L):
+        a = m.Attention(H, D, scale, KVH)
+        a.k_cache, a.v_cache = kv_cache[0, l], kv_cache[1, l]
+        layers.append(a)
+
+    q = torch.randn(B, H, D, device=dev).to(torch.bfloat16)
+    k = torch.randn(B, KVH, D, device=dev).to(torch.bfloat16)
+    v = torch.randn(B, KVH, D, device=dev).to(torch.bfloat16)
+    splits = args.splits or m.ops.decode_num_splits(B, KVH, nblk * BLOCK, dev)
+    ws_n = m.ops.decode_workspace_numel(B, H, D, splits)
+    workspace = torch.empty(max(ws_n, 1), dtype=torch.float32, device=dev)
+    outs = torch.empty(L, B, H, D, dtype=torch.bfloat16, device=dev)
+
+    def set_ctx():
+        m.set_context(False, slot_mapping=slot_mapping, context_lens=context_lens, block_tables=block_tables,
+                      decode_num_splits=splits, decode_workspace=workspace if splits > 1 else None)
+
+    def full_step():  # the hot path of one decode step: store + paged decode, every layer
+        for l, a in enumerate(layers):
+            outs[l] = a(q, k, v)
+
+    def decode_only():
+        for l, a in enumerate(layers):
+            m.paged_decode_attention(q, a.k_cache, a.v_cache, block_tables, context_lens, scale,
+                                     num_splits=splits, workspace=workspace if splits > 1 else None, out=outs[l])
+
+    def capture(fn):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            fn()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        gr = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gr):
+            fn()
+        return gr
+
+    set_ctx()
+    g_full = capture(full_step)
+    g_dec = capture(decode_only)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        barrier()
+        return ms / steps
+
+    with ClockSampler(local_rank) as clocks:
+        ms_step = timed(g_full.replay, args.steps, args.warmup)
+    ms_dec = timed(g_dec.replay, args.steps, args.warmup)
+
+    # ---- e2e: host buffers through Attention.forward, copies inside the timed region (eager launches)
+    hq = [torch.randn(B, H, D).to(torch.bfloat16).pin_memory() for _ in range(L)]
+    hk = [torch.randn(B, KVH, D).to(torch.bfloat16).pin_memory() for _ in range(L)]
+    hv = [torch.randn(B, KVH, D).to(torch.bfloat16).pin_memory() for _ in range(L)]
+    hout = [torch.empty(B, H, D, dtype=torch.bfloat16).pin_memory() for _ in range(L)]
+    h_slots, h_ctx, h_bt = slot_mapping.cpu().pin_memory(), context_lens.cpu().pin_memory(), block_tables.cpu().pin_memory()
+    d_slots, d_ctx, d_bt = torch.empty_like(slot_mapping), torch.empty_like(context_lens), torch.empty_like(block_tables)
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+
+    def e2e_step():
+        d_slots.copy_(h_slots, non_blocking=True)
+        d_ctx.copy_(h_ctx, non_blocking=True)
+        d_bt.copy_(h_bt, non_blocking=True)
+        m.set_context(False, slot_mapping=d_slots, context_lens=d_ctx, block_tables=d_bt,
+                      decode_num_splits=splits, decode_workspace=workspace if splits > 1 else None)
+        for l, a in enumerate(layers):
+            dq.copy_(hq[l], non_blocking=True)
+            dk.copy_(hk[l], non_blocking=True)
+            dv.copy_(hv[l], non_blocking=True)
+            hout[l].copy_(a(dq, dk, dv), non_blocking=True)
+
+    ms_e2e = timed(e2e_step, args.steps, args.warmup)
+    m.reset_context()
+    h2d = L * (hq[0].numel() + hk[0].numel() + hv[0].numel()) * 2 + (h_slots.numel() + h_ctx.numel() + h_bt.numel()) * 4
+    d2h = L * hout[0].numel() * 2
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    bytes_layer_rank = kv_bytes_per_layer(B, ctx, KVH, D)
+    bytes_step_job = bytes_layer_rank * L * tp
+    launches_per_step = L * (2 + (1 if splits > 1 else 0))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = bytes_layer_rank / (ms_dec / L * 1e-3) / 1e9
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "decode_traffic.json"))).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    line = {
+        "metric": METRIC, "value": bytes_step_job / (ms_step * 1e-3) / 1e9, "unit": "GB/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {
+            "workload": wl["name"], "layers": L, "batch": B, "context": ctx, "q_heads_per_rank": H,
+            "kv_heads_per_rank": KVH, "head_dim": D, "kvcache_block_size": BLOCK, "parallelism": f"tp{tp}",
+            "num_kv_splits": splits, "cuda_graph": True,
+            "l2": f"inputs ({2 * bytes_layer_rank * L / 1e9:.1f} GB of KV per rank per step) are >> 126 MB L2; no flush needed",
+        },
+        "tokens_per_s_attention_only": B / (ms_step * 1e-3),
+        "roofline": {
+            "bound": "hbm", "kernel": "paged_decode_kernel<bf16,128>", "achieved": achieved, "peak": peak,
+            "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s",
+            "frac_of_8TBps_spec": achieved / 8000.0,
+            "bytes_per_launch": bytes_layer_rank, "us_per_launch": ms_dec / L * 1e3,
+        },
+        "e2e": {"value": bytes_step_job / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "api": "minivllm_b200.Attention.forward per layer, pinned host q/k/v in, pinned host out"},
+        "gpu_launches": launches_per_step * args.steps,
+        "clocks": clocks.summary(),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        base = run_cpu_baseline(wl, steps=10, warmup=1)
+        line["cpu_baseline"] = {k_: base[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--splits", type=int, default=0, help="override the KV split count (0 = library heuristic)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl)
+    else:
+        run_b200(args, wl)
+
+
+if __name__ == "__main__":
+    main()

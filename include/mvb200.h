@@ -1,0 +1,134 @@
+/*
+ * mvb200.h — C ABI of the B200-native attention hot path for mini-vLLM.
+ *
+ * One shared library (libmvb200.so), plain pointers and sizes, no torch types.
+ * Every launcher is stateless and re-entrant: it enqueues kernels on `stream`
+ * (a cudaStream_t passed as void*), never allocates device memory, never
+ * synchronises the host, and is therefore CUDA-Graph capturable.  Return value:
+ * 0 on success, a non-zero MVB200_E* code otherwise; mvb200_last_error() gives
+ * the message for the calling thread.
+ *
+ * The reference (jianzhnie/mini-vllm) has no native code; each entry point
+ * replaces a Python/Triton/flash-attn call site of the reference, cited as
+ * file:line relative to the reference repository root.
+ *
+ * Layouts (all row-major, element strides unless said otherwise):
+ *   key/value/q/out : [N, heads, D], the two inner dims dense, row stride given
+ *   k_cache/v_cache : [NB, BS, KVH, D] contiguous            (inference_executor.py:209-221)
+ *   slot_mapping    : int32 [N], slot = block*BS + offset, <0 = skip (inference_executor.py:503-510,568-572)
+ *   block_tables    : int32 [S, MB] padded with -1            (inference_executor.py:619-688)
+ *   context_lens    : int32 [B], includes the current token   (inference_executor.py:566)
+ *   cu_seqlens_q/k  : int32 [S+1]                             (inference_executor.py:519-524)
+ */
+#ifndef MVB200_H_
+#define MVB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define MVB200_API __attribute__((visibility("default")))
+#else
+#define MVB200_API
+#endif
+
+#define MVB200_VERSION 100
+
+/* element types */
+#define MVB200_F32 0
+#define MVB200_F16 1
+#define MVB200_BF16 2
+
+/* error codes */
+#define MVB200_OK 0
+#define MVB200_EINVAL 1      /* bad argument (shape, stride, alignment, null pointer) */
+#define MVB200_EUNSUPPORTED 2 /* valid request this build has no kernel for */
+#define MVB200_ECUDA 3       /* CUDA runtime / driver error at launch */
+
+MVB200_API int mvb200_version(void);
+MVB200_API const char* mvb200_last_error(void);
+
+/* Name of the kernel family the last successful call on this thread dispatched to
+ * ("decode_tma_mma", "decode_generic", "prefill_tcgen05", "prefill_generic", "store_vec16", ...). */
+MVB200_API const char* mvb200_last_kernel(void);
+
+/*
+ * store_kvcache — scatter new K/V rows into the paged cache.
+ * Replaces StandardAttentionBackend.store_kv_cache (models/layers/attention_backend.py:196-266)
+ * and the Triton store_kvcache_kernel (models/layers/attention_backend.py:52-78, launch :225-234).
+ *
+ * For every i < num_tokens with 0 <= slot_mapping[i] < num_slots:
+ *   k_cache[slot_mapping[i], 0:row_elems] = key[i*key_row_stride + 0:row_elems]   (same for value)
+ * Bits are moved, never converted.  row_elems = KVH*D.
+ */
+MVB200_API int mvb200_store_kvcache(const void* key, const void* value,
+                         int64_t key_row_stride, int64_t value_row_stride,
+                         void* k_cache, void* v_cache,
+                         const int32_t* slot_mapping,
+                         int32_t num_tokens, int32_t row_elems, int64_t num_slots,
+                         int32_t dtype, void* stream);
+
+/*
+ * paged decode attention — one query token per sequence over its paged KV.
+ * Replaces flash_attn_with_kvcache(...) at models/layers/attention.py:439-447 and the eager
+ * PageAttention.__call__ (models/layers/page_attention.py:35-133).
+ *
+ * out[b,h,:] = softmax(scale * q[b,h,:] . K_b[0:ctx_b]^T) V_b[0:ctx_b],  kv head = h / (H/KVH).
+ * Rows with context_lens[b] <= 0 produce zeros.  Block-table entries that are negative inside
+ * the context contribute a zero key/value row (the eager reference's behaviour).
+ *
+ * num_splits >= 1 partitions every sequence's KV range over that many CTAs (grid is independent
+ * of the data, as CUDA Graph replay needs).  When num_splits > 1, `workspace` must hold
+ * mvb200_decode_workspace_bytes(B, H, D, num_splits) bytes; a second kernel reduces the splits.
+ */
+MVB200_API size_t mvb200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t head_dim,
+                                     int32_t num_splits);
+
+/* Split count the library recommends for a batch (>=1). max_context bounds the longest sequence. */
+MVB200_API int32_t mvb200_decode_suggest_splits(int32_t batch, int32_t num_kv_heads, int32_t max_context,
+                                     int32_t sm_count);
+
+MVB200_API int mvb200_paged_decode(const void* q, int64_t q_row_stride,
+                        const void* k_cache, const void* v_cache,
+                        const int32_t* block_tables, int64_t bt_row_stride,
+                        const int32_t* context_lens,
+                        void* out, int64_t out_row_stride,
+                        void* workspace, size_t workspace_bytes,
+                        int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
+                        int32_t block_size, int64_t num_blocks, int32_t max_blocks_per_seq,
+                        int32_t num_splits, float scale, int32_t dtype, void* stream);
+
+/*
+ * varlen causal prefill attention.
+ * Replaces flash_attn_varlen_func(...) at models/layers/attention.py:422-433 and the eager
+ * Attention._fallback_attention prefill branch (models/layers/attention.py:467-504).
+ *
+ * Sequence s owns query rows cu_seqlens_q[s]..cu_seqlens_q[s+1]-1 (Lq of them) and keys
+ * 0..Lk-1, Lk = cu_seqlens_k[s+1]-cu_seqlens_k[s].  Query i attends keys 0..(Lk-Lq)+i
+ * (bottom-right aligned causal mask, attention.py:584-587).
+ *
+ * Key/value source:
+ *   block_tables != NULL : key j of sequence s is k_cache[block_tables[s, j/BS], j%BS]
+ *                          (the prefix-cache path, attention.py:399-400); k/v are ignored.
+ *   block_tables == NULL : key j is k[(cu_seqlens_k[s]+j)*k_row_stride] (dense new-token K/V).
+ */
+MVB200_API int mvb200_prefill_varlen(const void* q, int64_t q_row_stride,
+                          const void* k, const void* v, int64_t k_row_stride, int64_t v_row_stride,
+                          int64_t num_kv_rows,
+                          const void* k_cache, const void* v_cache,
+                          const int32_t* block_tables, int64_t bt_row_stride,
+                          const int32_t* cu_seqlens_q, const int32_t* cu_seqlens_k,
+                          void* out, int64_t out_row_stride,
+                          int32_t num_seqs, int32_t total_q, int32_t max_seqlen_q, int32_t max_seqlen_k,
+                          int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
+                          int32_t block_size, int64_t num_blocks, int32_t max_blocks_per_seq,
+                          float scale, int32_t dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MVB200_H_ */

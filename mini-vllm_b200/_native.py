@@ -1,0 +1,85 @@
+"""ctypes binding of libmvb200.so (the C ABI declared in include/mvb200.h).
+
+The library is built in-tree by ``mini-vllm_b200/build.py`` (``__graft_entry__.build()``).
+There is no fallback: if the library is missing or a launcher reports an error the
+caller gets an exception.
+"""
+
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libmvb200.so")
+
+_lib = None
+
+# name -> (restype, argtypes); mirrors include/mvb200.h one to one
+SIGNATURES = {
+    "mvb200_version": (c_int32, []),
+    "mvb200_last_error": (c_char_p, []),
+    "mvb200_last_kernel": (c_char_p, []),
+    "mvb200_store_kvcache": (
+        c_int32,
+        [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
+         c_int32, c_int32, c_int64, c_int32, c_void_p],
+    ),
+    "mvb200_decode_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
+    "mvb200_decode_suggest_splits": (c_int32, [c_int32, c_int32, c_int32, c_int32]),
+    "mvb200_paged_decode": (
+        c_int32,
+        [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
+         c_void_p, c_int64, c_void_p, c_size_t,
+         c_int32, c_int32, c_int32, c_int32, c_int32, c_int64, c_int32,
+         c_int32, c_float, c_int32, c_void_p],
+    ),
+    "mvb200_prefill_varlen": (
+        c_int32,
+        [c_void_p, c_int64, c_void_p, c_void_p, c_int64, c_int64, c_int64,
+         c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p,
+         c_void_p, c_int64,
+         c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
+         c_int32, c_int64, c_int32, c_float, c_int32, c_void_p],
+    ),
+}
+
+
+class NativeLibraryError(RuntimeError):
+    pass
+
+
+def lib() -> ctypes.CDLL:
+    """Load libmvb200.so once; raise loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise NativeLibraryError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). The mvb200 ops have no CPU or PyTorch fallback."
+            )
+        handle = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)  # AttributeError if the .so is stale
+            fn.restype = res
+            fn.argtypes = args
+        _lib = handle
+    return _lib
+
+
+def last_error() -> str:
+    return (lib().mvb200_last_error() or b"").decode()
+
+
+def last_kernel() -> str:
+    return (lib().mvb200_last_kernel() or b"").decode()
+
+
+def check(rc: int, what: str) -> None:
+    if rc == 0:
+        return
+    msg = f"{what} failed (code {rc}): {last_error()}"
+    if rc == 1:
+        raise ValueError(msg)
+    raise RuntimeError(msg)

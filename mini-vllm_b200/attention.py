@@ -1,0 +1,159 @@
+"""Drop-in ``Attention`` layer backed by the sm_100a kernels.
+
+Same class surface as the reference's ``minivllm.models.layers.Attention``
+(attention.py:102-198): constructor ``(num_heads, head_dim, scale, num_kv_heads,
+use_buffered_page_attention=False)``, ``scale == 0 -> 1/sqrt(head_dim)`` (:154),
+attributes ``k_cache`` / ``v_cache`` (empty tensors until the executor assigns
+views of the paged cache, inference_executor.py:325-331) and
+``_cache_initialized``, ``forward(q, k, v) -> [N, H, D]``.  No parameters or
+buffers are registered, so ``load_weights`` / ``state_dict`` are unaffected.
+
+``forward`` keeps the reference's ordering contract (attention.py:225-455):
+cast to the cache dtype, store the new K/V through ``context.slot_mapping``,
+then attend — decode over ``block_tables``/``context_lens``, prefill over
+``cu_seqlens`` reading keys back through ``block_tables`` when they are present.
+"""
+
+from __future__ import annotations
+
+import math
+from typing import Callable
+
+import torch
+from torch import nn
+
+from . import context as _context
+from . import ops
+
+# Where forward() reads the per-step metadata from.  ``install_into_reference``
+# re-points this at the reference's own ContextVar accessor.
+_get_context: Callable[[], object] = _context.get_context
+
+
+def use_context_getter(getter: Callable[[], object]) -> None:
+    global _get_context
+    _get_context = getter
+
+
+class PagedDecodeAttention:
+    """Callable twin of the reference's ``PageAttention`` (page_attention.py:25-133)."""
+
+    def __call__(self, q, k_cache, v_cache, block_tables, context_lens, scale, **kw):
+        if k_cache.numel() == 0 or v_cache.numel() == 0:
+            raise ValueError("KV cache is empty — cannot compute page attention")
+        if block_tables.size(1) == 0:  # engine warm-up (page_attention.py:62-65)
+            return torch.zeros(q.size(0), q.size(1), q.size(2), device=q.device, dtype=q.dtype)
+        return ops.paged_decode_attention(q, k_cache, v_cache, block_tables, context_lens, scale, **kw)
+
+
+class B200AttentionBackend:
+    """Stands where the reference keeps ``self.backend`` (attention.py:157-173)."""
+
+    def store_kv_cache(self, key, value, k_cache, v_cache, slot_mapping) -> None:
+        ops.store_kvcache(key, value, k_cache, v_cache, slot_mapping)
+
+
+class Attention(nn.Module):
+    def __init__(
+        self,
+        num_heads: int,
+        head_dim: int,
+        scale: float,
+        num_kv_heads: int,
+        use_buffered_page_attention: bool = False,  # accepted for signature parity; one decode kernel
+    ) -> None:
+        super().__init__()
+        self.num_heads = num_heads
+        self.head_dim = head_dim
+        self.scale = float(scale) if scale != 0.0 else 1.0 / math.sqrt(head_dim)
+        self.num_kv_heads = num_kv_heads
+        self.backend = B200AttentionBackend()
+        self._page_attn = PagedDecodeAttention()
+        self.k_cache: torch.Tensor = torch.tensor([])
+        self.v_cache: torch.Tensor = torch.tensor([])
+        self._cache_initialized = False
+
+    def extra_repr(self) -> str:
+        return (
+            f"num_heads={self.num_heads}, head_dim={self.head_dim}, "
+            f"num_kv_heads={self.num_kv_heads}, scale={self.scale}, backend=mvb200(sm_100a)"
+        )
+
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+        context = _get_context()
+        k_cache, v_cache = self.k_cache, self.v_cache
+        has_cache = k_cache.numel() > 0 and v_cache.numel() > 0
+
+        if has_cache and q.dtype != k_cache.dtype:  # attention.py:229-234
+            q, k, v = q.to(k_cache.dtype), k.to(k_cache.dtype), v.to(k_cache.dtype)
+
+        if has_cache:
+            self._cache_initialized = True
+            slots = context.slot_mapping
+            if slots is not None and slots.numel() > 0:  # attention.py:237-243
+                ops.store_kvcache(k, v, k_cache, v_cache, slots)
+        elif not context.is_prefill and not self._cache_initialized:
+            raise RuntimeError(
+                "KV cache has not been initialized. Ensure ModelRunner.allocate_kv_cache() "
+                "is called before inference."
+            )
+
+        if context.is_prefill:
+            if context.cum_seqlens_q is None or context.cum_seqlens_k is None:
+                raise RuntimeError(
+                    "Cumulative sequence lengths not set in context for prefill phase. "
+                    "This is a bug in the inference pipeline."
+                )
+            paged = has_cache and context.block_tables is not None and context.block_tables.numel() > 0
+            return ops.prefill_varlen_attention(
+                q, k, v,
+                context.cum_seqlens_q, context.cum_seqlens_k,
+                context.max_seqlen_q, context.max_seqlen_k, self.scale,
+                k_cache=k_cache if paged else None,
+                v_cache=v_cache if paged else None,
+                block_tables=context.block_tables if paged else None,
+            )
+
+        if not self._cache_initialized:
+            raise RuntimeError(
+                "KV cache must be initialized before decode phase. "
+                "This indicates a problem with the inference pipeline."
+            )
+        if context.context_lens is None or context.block_tables is None:
+            raise RuntimeError(
+                "Context lengths or block tables not set for decode phase. "
+                "This is a bug in the inference pipeline."
+            )
+        return self._page_attn(
+            q, k_cache, v_cache, context.block_tables, context.context_lens, self.scale,
+            num_splits=getattr(context, "decode_num_splits", None),
+            workspace=getattr(context, "decode_workspace", None),
+        )
+
+
+def install_into_reference() -> None:
+    """Swap this layer into an importable ``minivllm`` (the reference) before models are built.
+
+    Every reference model imports the class by name from ``minivllm.models.layers``
+    (layers/__init__.py:22; qwen_base.py, opt.py, gpt2.py), so the name is rebound
+    in each of those modules, and ``forward`` is pointed at the reference's own
+    ``get_context`` so that its executor's ``set_context`` calls are seen.
+    """
+    import importlib
+
+    layers = importlib.import_module("minivllm.models.layers")
+    ref_ctx = importlib.import_module("minivllm.utils.context")
+    use_context_getter(ref_ctx.get_context)
+    layers.Attention = Attention
+    for name in (
+        "minivllm.models.layers.attention",
+        "minivllm.models.qwen_base",
+        "minivllm.models.opt",
+        "minivllm.models.gpt2",
+    ):
+        try:
+            mod = importlib.import_module(name)
+        except Exception:  # optional model files
+            continue
+        if hasattr(mod, "Attention"):
+            mod.Attention = Attention

@@ -1,0 +1,298 @@
+"""The three hot-path operators, called through the C ABI of libmvb200.so.
+
+Python keeps only what needs host knowledge: argument checks with the
+reference's exception types, stride bookkeeping, output/workspace allocation
+and the current CUDA stream.  Every tensor must live on a CUDA device; there is
+no CPU path.
+
+Reference call sites (relative to the reference repository):
+  store_kvcache              attention_backend.py:196-266 (+ Triton kernel :52-78)
+  paged_decode_attention     attention.py:439-447, page_attention.py:35-133
+  prefill_varlen_attention   attention.py:396-433, :467-504
+"""
+
+from __future__ import annotations
+
+import torch
+
+from . import _native
+
+_DTYPE_CODE = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+_SM_COUNT: dict[int, int] = {}
+
+
+def _code(dtype: torch.dtype) -> int:
+    try:
+        return _DTYPE_CODE[dtype]
+    except KeyError:
+        raise ValueError(f"mvb200: unsupported dtype {dtype}") from None
+
+
+def _require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "mvb200 ops run on CUDA tensors only (got a "
+                f"{t.device.type} tensor); there is no CPU fallback"
+            )
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _sm_count(device: torch.device) -> int:
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    if idx not in _SM_COUNT:
+        _SM_COUNT[idx] = torch.cuda.get_device_properties(idx).multi_processor_count
+    return _SM_COUNT[idx]
+
+
+def _rows(t: torch.Tensor) -> torch.Tensor:
+    """[N, heads, D] with dense inner dims (row stride free); copy only if needed."""
+    if t.dim() != 3:
+        raise ValueError(f"expected a [N, heads, head_dim] tensor, got shape {tuple(t.shape)}")
+    if t.size(0) > 0 and (t.stride(2) != 1 or t.stride(1) != t.size(2)):
+        t = t.contiguous()
+    return t
+
+
+def _row_stride(t: torch.Tensor) -> int:
+    return t.stride(0) if t.size(0) > 1 else t.size(1) * t.size(2)
+
+
+def _i32(t: torch.Tensor, device: torch.device) -> torch.Tensor:
+    if t.device != device:
+        t = t.to(device)
+    if t.dtype != torch.int32:
+        t = t.to(torch.int32)
+    return t
+
+
+# ---------------------------------------------------------------------------
+# store_kvcache
+# ---------------------------------------------------------------------------
+
+
+def store_kvcache(
+    key: torch.Tensor,
+    value: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    slot_mapping: torch.Tensor,
+) -> None:
+    """Scatter ``key[i]``/``value[i]`` to cache row ``slot_mapping[i]`` (``< 0`` skips).
+
+    Same contract as ``StandardAttentionBackend.store_kv_cache``
+    (attention_backend.py:196-266): ``ValueError`` when ``slot_mapping`` and the
+    batch disagree (:209-212); values are cast to the cache dtype first (:254-257).
+    """
+    _require_cuda(key, value, k_cache, v_cache, slot_mapping)
+    n, kvh, d = key.shape
+    if slot_mapping.numel() != n:
+        raise ValueError(f"slot_mapping size {slot_mapping.numel()} != batch_size {n}")
+    if value.shape != key.shape:
+        raise ValueError(f"key {tuple(key.shape)} and value {tuple(value.shape)} differ")
+    if n == 0:
+        return
+    if key.dtype != k_cache.dtype:
+        key = key.to(k_cache.dtype)
+    if value.dtype != v_cache.dtype:
+        value = value.to(v_cache.dtype)
+    if not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+        raise ValueError("k_cache / v_cache must be contiguous")
+    row = kvh * d
+    if k_cache.numel() % row or v_cache.numel() != k_cache.numel():
+        raise ValueError("cache size is not a multiple of num_kv_heads*head_dim")
+    key, value = _rows(key), _rows(value)
+    slots = _i32(slot_mapping.reshape(-1), key.device)
+    if not slots.is_contiguous():
+        slots = slots.contiguous()
+    rc = _native.lib().mvb200_store_kvcache(
+        key.data_ptr(), value.data_ptr(), _row_stride(key), _row_stride(value),
+        k_cache.data_ptr(), v_cache.data_ptr(), slots.data_ptr(),
+        n, row, k_cache.numel() // row, _code(k_cache.dtype), _stream(),
+    )
+    _native.check(rc, "mvb200_store_kvcache")
+
+
+# ---------------------------------------------------------------------------
+# paged decode attention
+# ---------------------------------------------------------------------------
+
+
+def decode_num_splits(batch: int, num_kv_heads: int, max_context: int, device: torch.device) -> int:
+    """Split count for a batch; fixed per captured batch size under CUDA Graphs."""
+    return int(_native.lib().mvb200_decode_suggest_splits(batch, num_kv_heads, max_context, _sm_count(device)))
+
+
+def decode_workspace_numel(batch: int, num_heads: int, head_dim: int, num_splits: int) -> int:
+    """float32 elements of split workspace (0 when ``num_splits == 1``)."""
+    return int(_native.lib().mvb200_decode_workspace_bytes(batch, num_heads, head_dim, num_splits)) // 4
+
+
+def paged_decode_attention(
+    q: torch.Tensor,
+    k_cache: torch.Tensor,
+    v_cache: torch.Tensor,
+    block_tables: torch.Tensor,
+    context_lens: torch.Tensor,
+    scale: float,
+    *,
+    num_splits: int | None = None,
+    workspace: torch.Tensor | None = None,
+    out: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """``softmax(scale * q K^T) V`` of one query token per sequence over paged KV.
+
+    ``q [B, H, D]``, caches ``[NB, BS, KVH, D]``, ``block_tables [B, MB]`` int32,
+    ``context_lens [B]`` int32 (current token included).  Returns ``[B, H, D]``.
+    Error contract follows ``PageAttention.__call__`` (page_attention.py:45-46,
+    :62-65) except for the data-dependent "no valid entry" check (:88-91), which
+    would need a host sync and is not capturable: such rows return zeros.
+    """
+    if k_cache.numel() == 0 or v_cache.numel() == 0:
+        raise ValueError("KV cache is empty — cannot compute page attention")
+    _require_cuda(q, k_cache, v_cache)
+    if k_cache.dim() != 4 or k_cache.shape != v_cache.shape:
+        raise ValueError("k_cache / v_cache must be [num_blocks, block_size, num_kv_heads, head_dim]")
+    if not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+        raise ValueError("k_cache / v_cache must be contiguous")
+    q = _rows(q)
+    b, h, d = q.shape
+    nb, bs, kvh, dc = k_cache.shape
+    if dc != d:
+        raise ValueError(f"head_dim mismatch: q has {d}, cache has {dc}")
+    if h % kvh:
+        raise ValueError(f"num_heads {h} is not a multiple of num_kv_heads {kvh}")
+    if q.dtype != k_cache.dtype:
+        q = q.to(k_cache.dtype)
+    if out is None:
+        out = torch.empty((b, h, d), dtype=q.dtype, device=q.device)
+    elif out.shape != (b, h, d) or out.dtype != q.dtype or not out.is_contiguous():
+        raise ValueError("out must be a contiguous [B, H, D] tensor of q's dtype")
+    if b == 0:
+        return out
+    block_tables = _i32(block_tables, q.device)
+    context_lens = _i32(context_lens.reshape(-1), q.device)
+    if block_tables.dim() != 2 or block_tables.size(0) != b or context_lens.numel() != b:
+        raise ValueError("block_tables must be [B, MB] and context_lens [B]")
+    mb = block_tables.size(1)
+    if mb > 0 and block_tables.stride(1) != 1:
+        block_tables = block_tables.contiguous()
+    if not context_lens.is_contiguous():
+        context_lens = context_lens.contiguous()
+    if num_splits is None:
+        num_splits = decode_num_splits(b, kvh, mb * bs, q.device) if mb > 0 else 1
+    ws_ptr, ws_bytes = 0, 0
+    if num_splits > 1 and mb > 0:
+        need = decode_workspace_numel(b, h, d, num_splits)
+        if workspace is None:
+            workspace = torch.empty(need, dtype=torch.float32, device=q.device)
+        elif workspace.numel() * workspace.element_size() < need * 4 or not workspace.is_contiguous():
+            raise ValueError(f"decode workspace too small: need {need} float32")
+        ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    rc = _native.lib().mvb200_paged_decode(
+        q.data_ptr(), _row_stride(q), k_cache.data_ptr(), v_cache.data_ptr(),
+        block_tables.data_ptr() if mb > 0 else 0, block_tables.stride(0) if mb > 0 else 0,
+        context_lens.data_ptr(), out.data_ptr(), h * d, ws_ptr, ws_bytes,
+        b, h, kvh, d, bs, nb, mb, num_splits, float(scale), _code(q.dtype), _stream(),
+    )
+    _native.check(rc, "mvb200_paged_decode")
+    return out
+
+
+# ---------------------------------------------------------------------------
+# varlen causal prefill attention
+# ---------------------------------------------------------------------------
+
+
+def prefill_varlen_attention(
+    q: torch.Tensor,
+    k: torch.Tensor | None,
+    v: torch.Tensor | None,
+    cu_seqlens_q: torch.Tensor,
+    cu_seqlens_k: torch.Tensor,
+    max_seqlen_q: int,
+    max_seqlen_k: int,
+    scale: float,
+    *,
+    k_cache: torch.Tensor | None = None,
+    v_cache: torch.Tensor | None = None,
+    block_tables: torch.Tensor | None = None,
+    out: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """Varlen causal attention over packed sequences (bottom-right aligned mask).
+
+    With ``block_tables`` the keys/values are the paged caches (prefix-cache
+    path, attention.py:399-400); without, the dense ``k``/``v`` rows addressed by
+    ``cu_seqlens_k`` (attention.py:481-488).  Returns ``[N, H, D]``.
+    """
+    _require_cuda(q, k, v, k_cache, v_cache, block_tables)
+    if cu_seqlens_q is None or cu_seqlens_k is None:
+        raise RuntimeError(
+            "Cumulative sequence lengths not set in context for prefill phase. "
+            "This is a bug in the inference pipeline."
+        )
+    q = _rows(q)
+    n, h, d = q.shape
+    if out is None:
+        out = torch.empty((n, h, d), dtype=q.dtype, device=q.device)
+    elif out.shape != (n, h, d) or out.dtype != q.dtype or not out.is_contiguous():
+        raise ValueError("out must be a contiguous [N, H, D] tensor of q's dtype")
+    cu_q = _i32(cu_seqlens_q.reshape(-1), q.device).contiguous()
+    cu_k = _i32(cu_seqlens_k.reshape(-1), q.device).contiguous()
+    s = cu_q.numel() - 1
+    if cu_k.numel() != s + 1:
+        raise ValueError("cu_seqlens_q and cu_seqlens_k must have the same length")
+    if n == 0 or s <= 0:
+        return out
+    paged = block_tables is not None and block_tables.numel() > 0
+    if paged:
+        if k_cache is None or v_cache is None or k_cache.numel() == 0:
+            raise ValueError("block_tables given but the KV cache is empty")
+        if not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+            raise ValueError("k_cache / v_cache must be contiguous")
+        nb, bs, kvh, dc = k_cache.shape
+        if q.dtype != k_cache.dtype:
+            q = q.to(k_cache.dtype)
+            out_cast = out
+            out = torch.empty_like(q)
+        else:
+            out_cast = None
+        bt = _i32(block_tables, q.device)
+        if bt.stride(1) != 1:
+            bt = bt.contiguous()
+        if bt.size(0) != s:
+            raise ValueError("block_tables must have one row per sequence")
+        args_kv = (0, 0, 0, 0, 0, k_cache.data_ptr(), v_cache.data_ptr(), bt.data_ptr(), bt.stride(0))
+        mb = bt.size(1)
+    else:
+        if k is None or v is None:
+            raise ValueError("dense prefill needs k and v")
+        k, v = _rows(k), _rows(v)
+        if k.dtype != q.dtype or v.dtype != q.dtype:
+            k, v = k.to(q.dtype), v.to(q.dtype)
+        kvh, dc = k.size(1), k.size(2)
+        nb, bs, mb = 0, 0, 0
+        out_cast = None
+        args_kv = (k.data_ptr(), v.data_ptr(), _row_stride(k), _row_stride(v), k.size(0), 0, 0, 0, 0)
+    if dc != d:
+        raise ValueError(f"head_dim mismatch: q has {d}, k/v have {dc}")
+    if h % kvh:
+        raise ValueError(f"num_heads {h} is not a multiple of num_kv_heads {kvh}")
+    rc = _native.lib().mvb200_prefill_varlen(
+        q.data_ptr(), _row_stride(q), *args_kv, cu_q.data_ptr(), cu_k.data_ptr(),
+        out.data_ptr(), h * d, s, n, int(max_seqlen_q), int(max_seqlen_k),
+        h, kvh, d, bs, nb, mb, float(scale), _code(q.dtype), _stream(),
+    )
+    _native.check(rc, "mvb200_prefill_varlen")
+    if out_cast is not None:
+        out_cast.copy_(out)
+        return out_cast
+    return out
+
+
+def last_kernel() -> str:
+    """Kernel family the last call on this thread dispatched to (for tests / bench)."""
+    return _native.last_kernel()

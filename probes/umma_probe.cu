@@ -1,0 +1,163 @@
+// umma_probe.cu — hardware probe for the tcgen05 building blocks the prefill kernel relies on.
+// Runs five single-CTA experiments and prints the max error of each against a host reference:
+//   0  S = A * B^T          A, B K-major in smem (128B swizzle, TMA-loaded)          [Q K^T]
+//   1  O = A * B            B MN-major, descriptor LBO=16384 SBO=1024                [P V, SS]
+//   2  O = A * B            B MN-major, descriptor LBO=1024  SBO=16384               (alt. encoding)
+//   3  O = A * B            A from TMEM (bf16 packed by tcgen05.st), B as in 1       [P V, TS]
+//   4  O = A * B            A from TMEM, B as in 2
+// Build: make -C probes        Run (B200): probes/umma_probe
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../mini-vllm_b200/csrc/tcgen05.cuh"
+
+using namespace mvb200;
+
+constexpr int M = 128, N = 128, K = 128;
+constexpr int kHalfBytes = 128 * 128;  // [128 rows][128 B]
+
+__global__ void __launch_bounds__(128)
+probe_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+             const __nv_bfloat16* __restrict__ a_gmem, float* __restrict__ out, int variant) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sA = base, sB = base + 2 * kHalfBytes;
+  const uint32_t bar_tma = sB + 2 * kHalfBytes, bar_mma = bar_tma + 8, slot = bar_tma + 16;
+  volatile uint32_t* slot_gen = reinterpret_cast<volatile uint32_t*>(smem_raw + (slot - smem_u32(smem_raw)));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0) {
+    tmem_alloc(slot, 256);
+    tmem_relinquish();
+  }
+  if (threadIdx.x == 0) {
+    mbar_init(bar_tma, 1);
+    mbar_init(bar_mma, 1);
+    fence_mbar_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *slot_gen;
+
+  if (threadIdx.x == 0) {
+    mbar_arrive_expect_tx(bar_tma, 4 * kHalfBytes);
+    for (int h = 0; h < 2; ++h) {
+      tma_load_2d(sA + h * kHalfBytes, &tmap_a, bar_tma, h * 64, 0);
+      tma_load_2d(sB + h * kHalfBytes, &tmap_b, bar_tma, h * 64, 0);
+    }
+  }
+  mbar_wait(bar_tma, 0);
+
+  const bool ts = variant >= 3;
+  const uint32_t tP = tmem + 128;  // P columns (bf16 pairs) for the TS variants
+  if (ts) {
+    // every thread owns one row of A: pack bf16 pairs into 64 TMEM columns
+    const int row = threadIdx.x;
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(a_gmem + (size_t)row * K);
+    const uint32_t lane_addr = tP + ((uint32_t)(32 * warp) << 16);
+    for (int c = 0; c < 64; c += 32) {
+      uint32_t r[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) r[i] = src[c + i];
+      tmem_st32(lane_addr + c, r);
+    }
+    tmem_wait_st();
+    tc_fence_before();
+    __syncthreads();
+  }
+
+  if (threadIdx.x == 0) {
+    tc_fence_after();
+    const bool b_mn = variant >= 1;
+    const uint32_t idesc = umma_idesc(M, N, true, false, b_mn);
+    const bool alt = (variant == 2 || variant == 4);
+    for (int kk = 0; kk < K / 16; ++kk) {
+      // A (K-major): 16 elements = 32 B inside the 128 B swizzle row, next 64 elements = next half
+      const uint64_t a_desc = umma_smem_desc(sA + (kk >> 2) * kHalfBytes + (kk & 3) * 32, 16, 1024);
+      uint64_t b_desc;
+      if (!b_mn) {
+        b_desc = umma_smem_desc(sB + (kk >> 2) * kHalfBytes + (kk & 3) * 32, 16, 1024);
+      } else {
+        // B (MN-major): rows are k (tokens), 128 B = 64 n; 16 k rows = 2048 B; n halves 16384 B apart
+        const uint32_t addr = sB + kk * 16 * 128;
+        b_desc = alt ? umma_smem_desc(addr, 1024, kHalfBytes) : umma_smem_desc(addr, kHalfBytes, 1024);
+      }
+      if (ts) umma_ts(tmem, tP + kk * 8, b_desc, idesc, kk > 0);
+      else    umma_ss(tmem, a_desc, b_desc, idesc, kk > 0);
+    }
+    umma_commit(bar_mma);
+  }
+  mbar_wait(bar_mma, 0);
+  tc_fence_after();
+
+  const int row = threadIdx.x;
+  const uint32_t lane_addr = tmem + ((uint32_t)(32 * warp) << 16);
+  for (int c = 0; c < N; c += 32) {
+    uint32_t r[32];
+    tmem_ld32(lane_addr + c, r);
+    tmem_wait_ld();
+#pragma unroll
+    for (int i = 0; i < 32; ++i) out[(size_t)row * N + c + i] = __uint_as_float(r[i]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 256);
+  (void)lane;
+}
+
+static float bf(uint16_t b) { uint32_t u = (uint32_t)b << 16; float f; memcpy(&f, &u, 4); return f; }
+static uint16_t tobf(float f) { uint32_t u; memcpy(&u, &f, 4); return (uint16_t)(u >> 16); }
+
+int main() {
+  std::vector<uint16_t> A(M * K), B(N * K);
+  srand(7);
+  for (auto& x : A) x = tobf((float)(rand() % 9 - 4) / 4.f);
+  for (auto& x : B) x = tobf((float)(rand() % 9 - 4) / 4.f);
+  __nv_bfloat16 *dA, *dB;
+  float* dO;
+  cudaMalloc(&dA, A.size() * 2);
+  cudaMalloc(&dB, B.size() * 2);
+  cudaMalloc(&dO, M * N * 4);
+  cudaMemcpy(dA, A.data(), A.size() * 2, cudaMemcpyHostToDevice);
+  cudaMemcpy(dB, B.data(), B.size() * 2, cudaMemcpyHostToDevice);
+  CUtensorMap ma, mb;
+  const uint64_t dims[2] = {128, 128};
+  const uint64_t str[2] = {0, 256};
+  const uint32_t box[2] = {64, 128};
+  if (make_tensor_map(&ma, dA, 2, 2, dims, str, box, true) || make_tensor_map(&mb, dB, 2, 2, dims, str, box, true)) {
+    printf("tensor map failed: %s\n", mvb200_last_error());
+    return 1;
+  }
+  const int smem = 4 * kHalfBytes + 64 + 1024;
+  cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  std::vector<float> O(M * N);
+  int bad = 0;
+  for (int variant = 0; variant < 5; ++variant) {
+    cudaMemset(dO, 0, M * N * 4);
+    probe_kernel<<<1, 128, smem>>>(ma, mb, dA, dO, variant);
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+      printf("variant %d: CUDA error %s\n", variant, cudaGetErrorString(e));
+      return 2;
+    }
+    cudaMemcpy(O.data(), dO, M * N * 4, cudaMemcpyDeviceToHost);
+    double maxerr = 0;
+    for (int i = 0; i < M; ++i)
+      for (int j = 0; j < N; ++j) {
+        double ref = 0;
+        for (int k = 0; k < K; ++k)
+          ref += variant == 0 ? (double)bf(A[i * K + k]) * bf(B[j * K + k])   // A B^T
+                              : (double)bf(A[i * K + k]) * bf(B[k * N + j]);  // A B
+        double err = fabs(ref - O[i * N + j]);
+        if (err > maxerr) maxerr = err;
+      }
+    printf("variant %d: max abs err %.4g  %s   (O[0][0..3] = %g %g %g %g)\n", variant, maxerr,
+           maxerr < 1e-3 ? "OK" : "MISMATCH", O[0], O[1], O[2], O[3]);
+    if (maxerr >= 1e-3) ++bad;
+  }
+  printf("probe done: %d mismatching variants (expected: 0,1,3 OK or 0,2,4 OK)\n", bad);
+  return 0;
+}

@@ -1,0 +1,83 @@
+"""The C-ABI library: it loads on a CPU-only box and exports what include/mvb200.h declares."""
+
+import ctypes
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def native():
+    import __graft_entry__ as entry
+
+    entry.build()
+    import minivllm_b200
+
+    return minivllm_b200._native
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "mvb200.h")).read()
+    return sorted(set(re.findall(r"MVB200_API[^;(]*?\b(mvb200_\w+)\s*\(", text)))
+
+
+def test_header_declares_the_hot_path():
+    syms = _declared_symbols()
+    for want in ("mvb200_store_kvcache", "mvb200_paged_decode", "mvb200_prefill_varlen",
+                 "mvb200_decode_workspace_bytes", "mvb200_decode_suggest_splits",
+                 "mvb200_version", "mvb200_last_error", "mvb200_last_kernel"):
+        assert want in syms
+
+
+def test_library_exports_every_declared_symbol(native):
+    handle = ctypes.CDLL(native.LIB_PATH)
+    for sym in _declared_symbols():
+        assert hasattr(handle, sym), f"{sym} declared in mvb200.h but not exported"
+    assert sorted(native.SIGNATURES) == _declared_symbols()
+    assert native.lib().mvb200_version() == 100
+
+
+def test_host_side_helpers_need_no_gpu(native):
+    lib = native.lib()
+    # workspace: B*H*S*(D+1) floats when S > 1, nothing for a single split
+    assert lib.mvb200_decode_workspace_bytes(256, 16, 128, 1) == 0
+    assert lib.mvb200_decode_workspace_bytes(256, 16, 128, 4) == 256 * 16 * 4 * 129 * 4
+    # plenty of (sequence, kv head) units -> no split; one long sequence -> many splits
+    assert lib.mvb200_decode_suggest_splits(256, 8, 2048, 148) == 1
+    s = lib.mvb200_decode_suggest_splits(1, 4, 32768, 148)
+    assert 32 <= s <= 128
+    assert lib.mvb200_decode_suggest_splits(1, 1, 64, 148) == 1
+
+
+def test_argument_errors_are_reported_without_a_gpu(native):
+    lib = native.lib()
+    rc = lib.mvb200_store_kvcache(None, None, 8, 8, None, None, None, 4, 8, 16, 0, None)
+    assert rc == 1 and "null" in native.last_error()
+    rc = lib.mvb200_store_kvcache(None, None, 8, 8, None, None, None, 4, 8, 16, 9, None)
+    assert rc == 1
+    rc = lib.mvb200_paged_decode(None, 0, None, None, None, 0, None, None, 0, None, 0,
+                                 2, 7, 2, 128, 64, 10, 4, 1, 1.0, 2, None)
+    assert rc == 1 and "multiple" in native.last_error()
+    with pytest.raises(ValueError):
+        native.check(1, "x")
+    with pytest.raises(RuntimeError):
+        native.check(3, "x")
+
+
+def test_ops_refuse_cpu_tensors(native):
+    import torch
+
+    import minivllm_b200 as m
+
+    z = torch.zeros(1, 1, 8)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m.store_kvcache(z, z, torch.zeros(4, 8), torch.zeros(4, 8), torch.zeros(1, dtype=torch.int32))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m.paged_decode_attention(z, torch.zeros(2, 4, 1, 8), torch.zeros(2, 4, 1, 8),
+                                 torch.zeros(1, 1, dtype=torch.int32), torch.ones(1, dtype=torch.int32), 1.0)
+    with pytest.raises(ValueError, match="empty"):
+        m.paged_decode_attention(z, torch.tensor([]), torch.tensor([]),
+                                 torch.zeros(1, 1, dtype=torch.int32), torch.ones(1, dtype=torch.int32), 1.0)

@@ -1,0 +1,400 @@
+"""Parity of the CUDA path (through the C ABI) against the golden vectors and the CPU oracle.
+
+Run on the B200 box: ``python -m pytest tests -m gpu``.
+Tolerances: store is bit-exact; attention max-abs <= 2e-2 for bf16 (BASELINE.json
+north_star), 4e-3 for fp16, 2e-5 for fp32 (the reference's own tests use
+rtol 1e-4 / atol 1e-5 on fp32, tests/test_page_attention.py:120).
+"""
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import paged_attention_oracle as orc
+from tests.conftest import golden_to_float, golden_to_torch, load_golden
+
+pytestmark = pytest.mark.gpu
+
+TOL = {"f32": 2e-5, "f16": 4e-3, "bf16": 2e-2}
+TDT = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}
+
+
+def _cases(name):
+    return [str(c) for c in load_golden(name)["cases"]]
+
+
+def _f32(t: torch.Tensor) -> np.ndarray:
+    return t.detach().float().cpu().numpy()
+
+
+def _bits(t: torch.Tensor) -> np.ndarray:
+    return t.detach().contiguous().cpu().view(torch.uint8).numpy()
+
+
+@pytest.fixture(scope="module")
+def m(cuda_device):
+    import minivllm_b200
+
+    return minivllm_b200
+
+
+# ---------------------------------------------------------------------------
+# store_kvcache: bit-exact
+# ---------------------------------------------------------------------------
+
+
+@pytest.mark.parametrize("case", _cases("store"))
+def test_store_golden_bit_exact(m, cuda_device, case):
+    g = load_golden("store")
+    dt = str(g[f"{case}.dtype"])
+    n, kvh, d, slots_n, strided = (int(x) for x in g[f"{case}.meta"])
+    key = golden_to_torch(g[f"{case}.key"], dt, cuda_device)
+    value = golden_to_torch(g[f"{case}.value"], dt, cuda_device)
+    if strided:  # rebuild row-strided views of a fused buffer, as the model produces them
+        fused = torch.zeros(n, 3 * kvh * d + 8, dtype=key.dtype, device=cuda_device)
+        fused[:, kvh * d : 2 * kvh * d] = key.view(n, -1)
+        fused[:, 2 * kvh * d : 3 * kvh * d] = value.view(n, -1)
+        key = fused[:, kvh * d : 2 * kvh * d].view(n, kvh, d)
+        value = fused[:, 2 * kvh * d : 3 * kvh * d].view(n, kvh, d)
+        assert not key.is_contiguous() or n == 1
+    kc = golden_to_torch(g[f"{case}.k_cache_in"], dt, cuda_device)
+    vc = golden_to_torch(g[f"{case}.v_cache_in"], dt, cuda_device)
+    slots = torch.from_numpy(g[f"{case}.slots"]).to(cuda_device)
+    m.store_kvcache(key, value, kc, vc, slots)
+    torch.cuda.synchronize()
+    assert np.array_equal(_bits(kc).ravel(), g[f"{case}.k_cache_out"].view(np.uint8).ravel())
+    assert np.array_equal(_bits(vc).ravel(), g[f"{case}.v_cache_out"].view(np.uint8).ravel())
+    assert m.ops.last_kernel().startswith("store_vec")
+
+
+def test_store_mismatch_raises(m, cuda_device):
+    k = torch.zeros(3, 2, 8, device=cuda_device)
+    c = torch.zeros(8, 16, device=cuda_device)
+    with pytest.raises(ValueError, match="slot_mapping size"):
+        m.store_kvcache(k, k, c, c.clone(), torch.tensor([1, 2], device=cuda_device, dtype=torch.int32))
+
+
+@pytest.mark.parametrize("n,kvh", [(256, 8), (8192, 8), (16384, 1)])
+def test_store_full_size_roundtrip(m, cuda_device, n, kvh):
+    """BASELINE sizes (cfg2 decode N=256, cfg3 prefill N=8192, cfg5 N=16384/rank): scatter then
+    gather must return the inputs bit-for-bit and leave every other slot untouched."""
+    d, bs = 128, 64
+    g = torch.Generator(device="cpu").manual_seed(n + kvh)
+    nblocks = n // bs + 40
+    key = torch.randn(n, kvh, d, generator=g).to(torch.bfloat16).to(cuda_device)
+    fused = torch.randn(n, 2 * kvh * d, generator=g).to(torch.bfloat16).to(cuda_device)
+    value = fused[:, kvh * d :].view(n, kvh, d)  # row-strided like the model's v
+    perm = torch.randperm(nblocks * bs, generator=g)[:n].to(torch.int32)
+    perm[::97] = -1
+    slots = perm.to(cuda_device)
+    kc = torch.full((nblocks, bs, kvh, d), 7.0, dtype=torch.bfloat16, device=cuda_device)
+    vc = torch.full((nblocks, bs, kvh, d), -3.0, dtype=torch.bfloat16, device=cuda_device)
+    m.store_kvcache(key, value, kc, vc, slots)
+    valid = slots >= 0
+    idx = slots[valid].long()
+    assert torch.equal(kc.view(-1, kvh, d)[idx], key[valid])
+    assert torch.equal(vc.view(-1, kvh, d)[idx], value[valid])
+    untouched = torch.ones(nblocks * bs, dtype=torch.bool, device=cuda_device)
+    untouched[idx] = False
+    assert (kc.view(-1, kvh * d)[untouched] == 7.0).all()
+    assert (vc.view(-1, kvh * d)[untouched] == -3.0).all()
+
+
+# ---------------------------------------------------------------------------
+# paged decode
+# ---------------------------------------------------------------------------
+
+
+def _decode_inputs(g, case, device):
+    dt = str(g[f"{case}.dtype"])
+    return (
+        dt,
+        golden_to_torch(g[f"{case}.q"], dt, device),
+        golden_to_torch(g[f"{case}.k_cache"], dt, device),
+        golden_to_torch(g[f"{case}.v_cache"], dt, device),
+        torch.from_numpy(g[f"{case}.block_tables"]).to(device),
+        torch.from_numpy(g[f"{case}.context_lens"]).to(device),
+        float(g[f"{case}.scale"]),
+    )
+
+
+@pytest.mark.parametrize("case", _cases("decode"))
+def test_decode_golden(m, cuda_device, case):
+    g = load_golden("decode")
+    dt, q, kc, vc, bt, ctx, scale = _decode_inputs(g, case, cuda_device)
+    out = m.paged_decode_attention(q, kc, vc, bt, ctx, scale)
+    torch.cuda.synchronize()
+    kern = m.ops.last_kernel()
+    fast = dt != "f32" and kc.size(1) % 64 == 0 and kc.size(3) in (64, 128)
+    assert kern == ("decode_tma_mma" if fast else "decode_generic"), kern
+    assert out.dtype == q.dtype and out.shape == q.shape
+    ref = golden_to_float(g[f"{case}.out"], dt)
+    err = np.abs(_f32(out) - ref)
+    assert err.max() <= TOL[dt], (case, err.max(), err.mean())
+    # and against the float64 oracle on the same inputs
+    o = orc.paged_decode(_f32(q), _f32(kc), _f32(vc), g[f"{case}.block_tables"], g[f"{case}.context_lens"], scale)
+    assert np.abs(_f32(out) - o).max() <= TOL[dt]
+
+
+@pytest.mark.parametrize("case", ["qwen3_g2", "qwen3_g4", "qwen2_g7", "qwen2_g8", "opt_mha"])
+@pytest.mark.parametrize("splits", [1, 2, 3, 9])
+def test_decode_split_kv_invariance(m, cuda_device, case, splits):
+    g = load_golden("decode")
+    dt, q, kc, vc, bt, ctx, scale = _decode_inputs(g, case, cuda_device)
+    out = m.paged_decode_attention(q, kc, vc, bt, ctx, scale, num_splits=splits)
+    assert m.ops.last_kernel() == "decode_tma_mma"
+    ref = golden_to_float(g[f"{case}.out"], dt)
+    assert np.abs(_f32(out) - ref).max() <= TOL[dt]
+
+
+def test_decode_padding_rows_and_stale_columns(m, cuda_device):
+    """CUDA-Graph replay shape: full-width table with stale ids beyond the live columns,
+    padded rows with context_len == 0 (inference_executor.py:751-768) -> zeros, no fault."""
+    g = load_golden("decode")
+    dt, q, kc, vc, bt, ctx, scale = _decode_inputs(g, "qwen3_g2", cuda_device)
+    b, mb = bt.shape
+    wide = torch.full((b + 3, mb + 20), 10**6, dtype=torch.int32, device=cuda_device)  # garbage ids
+    wide[:b, :mb] = bt
+    ctx2 = torch.zeros(b + 3, dtype=torch.int32, device=cuda_device)
+    ctx2[:b] = ctx
+    q2 = torch.randn(b + 3, q.size(1), q.size(2), device=cuda_device).to(q.dtype)
+    q2[:b] = q
+    for splits in (1, 4):
+        out = m.paged_decode_attention(q2, kc, vc, wide, ctx2, scale, num_splits=splits)
+        ref = golden_to_float(g["qwen3_g2.out"], dt)
+        assert np.abs(_f32(out[:b]) - ref).max() <= TOL[dt]
+        assert not out[b:].float().abs().any()
+
+
+def test_decode_nan_garbage_beyond_context_is_ignored(m, cuda_device):
+    """torch.empty caches can hold NaN bit patterns in never-written slots."""
+    g = load_golden("decode")
+    dt, q, kc, vc, bt, ctx, scale = _decode_inputs(g, "qwen3_g4", cuda_device)
+    kc, vc = kc.clone(), vc.clone()
+    bs = kc.size(1)
+    for b in range(bt.size(0)):
+        c = int(ctx[b])
+        last = int(bt[b, (c - 1) // bs])
+        if c % bs:
+            kc[last, c % bs :] = float("nan")
+            vc[last, c % bs :] = float("nan")
+    out = m.paged_decode_attention(q, kc, vc, bt, ctx, scale)
+    ref = golden_to_float(g["qwen3_g4.out"], dt)
+    assert np.abs(_f32(out) - ref).max() <= TOL[dt]
+
+
+def test_decode_error_contracts(m, cuda_device):
+    q = torch.randn(2, 8, 64, device=cuda_device)
+    empty = torch.tensor([], device=cuda_device)
+    bt = torch.zeros(2, 2, dtype=torch.int32, device=cuda_device)
+    ctx = torch.tensor([8, 8], dtype=torch.int32, device=cuda_device)
+    with pytest.raises(ValueError, match="empty"):
+        m.PagedDecodeAttention()(q, empty, empty, bt, ctx, 0.125)
+    kc = torch.randn(4, 16, 8, 64, device=cuda_device)
+    z = m.PagedDecodeAttention()(q, kc, kc, bt[:, :0], ctx, 0.125)
+    assert z.shape == (2, 8, 64) and not z.any()
+    # int64 index tensors are accepted like the reference's tests pass them
+    out = m.paged_decode_attention(q, kc, kc, bt.long(), ctx.long(), 0.125)
+    assert out.shape == (2, 8, 64)
+
+
+def _random_paged(device, batch, ctxs, kvh, d, bs, dtype, seed, extra_blocks=8):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    nblk = [(c + bs - 1) // bs for c in ctxs]
+    total = sum(nblk) + extra_blocks
+    perm = torch.randperm(total, generator=g)
+    mb = max(nblk)
+    bt = torch.full((batch, mb), -1, dtype=torch.int32)
+    c0 = 0
+    for b, nb in enumerate(nblk):
+        bt[b, :nb] = perm[c0 : c0 + nb]
+        c0 += nb
+    kc = torch.empty(total, bs, kvh, d, dtype=dtype, device=device).normal_(generator=None)
+    vc = torch.empty(total, bs, kvh, d, dtype=dtype, device=device).normal_(generator=None)
+    return kc, vc, bt.to(device), torch.tensor(ctxs, dtype=torch.int32, device=device)
+
+
+@pytest.mark.parametrize(
+    "name,batch,ctx,h,kvh",
+    [
+        ("cfg2_qwen3_0.6b", 256, 2048, 16, 8),
+        ("cfg4_qwen2_7b_32k", 2, 32768, 28, 4),
+        ("cfg5_qwen2_72b_rank", 512, 1024, 8, 1),
+    ],
+)
+def test_decode_full_size_against_oracle_samples(m, cuda_device, name, batch, ctx, h, kvh):
+    """BASELINE.json sizes: oracle on sampled sequences + split-count invariance on all rows."""
+    torch.manual_seed(batch + ctx)
+    d, bs = 128, 64
+    rng = np.random.default_rng(3)
+    ctxs = [int(x) for x in rng.integers(max(1, ctx // 2), ctx + 1, size=batch)]
+    ctxs[0] = ctx
+    kc, vc, bt, cl = _random_paged(cuda_device, batch, ctxs, kvh, d, bs, torch.bfloat16, 11)
+    q = torch.randn(batch, h, d, device=cuda_device).to(torch.bfloat16)
+    scale = d**-0.5
+    out = m.paged_decode_attention(q, kc, vc, bt, cl, scale)
+    assert m.ops.last_kernel() == "decode_tma_mma"
+    out_s = m.paged_decode_attention(q, kc, vc, bt, cl, scale, num_splits=5)
+    assert (out.float() - out_s.float()).abs().max().item() <= 1e-2
+    for b in (0, batch // 2, batch - 1):
+        blocks = bt[b, : (ctxs[b] + bs - 1) // bs].long()
+        kk = _f32(kc[blocks])
+        vv = _f32(vc[blocks])
+        local_bt = np.arange(blocks.numel(), dtype=np.int32)[None, :]
+        o = orc.paged_decode(_f32(q[b : b + 1]), kk, vv, local_bt, np.array([ctxs[b]]), scale)
+        err = np.abs(_f32(out[b : b + 1]) - o)
+        assert err.max() <= TOL["bf16"], (name, b, err.max())
+
+
+def test_decode_cuda_graph_capture_and_replay(m, cuda_device):
+    """Capture once with static buffers, replay with different lengths/tables (T5)."""
+    d, bs, h, kvh, batch, mb = 128, 64, 16, 8, 8, 16
+    ctxs = [100, 513, 64, 1, 700, 1000, 65, 300]
+    kc, vc, bt, cl = _random_paged(cuda_device, batch, ctxs, kvh, d, bs, torch.bfloat16, 5)
+    q = torch.randn(batch, h, d, device=cuda_device).to(torch.bfloat16)
+    st_q = torch.zeros_like(q)
+    st_bt = torch.zeros(batch, mb, dtype=torch.int32, device=cuda_device)
+    st_cl = torch.zeros(batch, dtype=torch.int32, device=cuda_device)
+    st_out = torch.zeros_like(q)
+    splits = 3
+    ws = torch.empty(m.ops.decode_workspace_numel(batch, h, d, splits), device=cuda_device)
+    scale = d**-0.5
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        m.paged_decode_attention(st_q, kc, vc, st_bt, st_cl, scale, num_splits=splits, workspace=ws, out=st_out)
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        m.paged_decode_attention(st_q, kc, vc, st_bt, st_cl, scale, num_splits=splits, workspace=ws, out=st_out)
+    for shift in (0, 37):
+        ctx_now = [max(1, c - shift) for c in ctxs]
+        st_q.copy_(q)
+        st_bt.zero_()
+        st_bt[:, : bt.size(1)] = bt.clamp(min=0)
+        st_cl.copy_(torch.tensor(ctx_now, dtype=torch.int32))
+        graph.replay()
+        torch.cuda.synchronize()
+        eager = m.paged_decode_attention(q, kc, vc, bt, torch.tensor(ctx_now, dtype=torch.int32, device=cuda_device), scale, num_splits=1)
+        assert (st_out.float() - eager.float()).abs().max().item() <= 1e-2
+        o = orc.paged_decode(_f32(q[:2]), _f32(kc), _f32(vc), bt[:2].cpu().numpy(), np.array(ctx_now[:2]), scale)
+        assert np.abs(_f32(st_out[:2]) - o).max() <= TOL["bf16"]
+
+
+# ---------------------------------------------------------------------------
+# prefill
+# ---------------------------------------------------------------------------
+
+
+@pytest.mark.parametrize("case", _cases("prefill"))
+def test_prefill_dense_golden(m, cuda_device, case):
+    g = load_golden("prefill")
+    dt = str(g[f"{case}.dtype"])
+    q = golden_to_torch(g[f"{case}.q"], dt, cuda_device)
+    k = golden_to_torch(g[f"{case}.k"], dt, cuda_device)
+    v = golden_to_torch(g[f"{case}.v"], dt, cuda_device)
+    cu = torch.from_numpy(g[f"{case}.cu_seqlens"]).to(cuda_device)
+    lens = np.diff(g[f"{case}.cu_seqlens"])
+    scale = float(g[f"{case}.scale"])
+    out = m.prefill_varlen_attention(q, k, v, cu, cu, int(lens.max()), int(lens.max()), scale)
+    ref = golden_to_float(g[f"{case}.out"], dt)
+    o = orc.prefill_dense(_f32(q), _f32(k), _f32(v), g[f"{case}.cu_seqlens"], g[f"{case}.cu_seqlens"], scale)
+    err = np.abs(_f32(out) - o)
+    assert err.max() <= TOL[dt], (case, m.ops.last_kernel(), err.max(), err.mean())
+    assert np.abs(_f32(out) - ref).max() <= 2 * TOL[dt]  # the reference rounds its scores to bf16
+
+
+@pytest.mark.parametrize("dtype,h,kvh,d", [("bf16", 8, 2, 128), ("bf16", 7, 1, 128), ("f16", 4, 4, 64), ("f32", 4, 2, 64)])
+def test_prefill_prefix_hits_equal_suffix_of_full_prefill(m, cuda_device, dtype, h, kvh, d):
+    """P1: queries of the uncached suffix, keys read through block_tables (50 % hits)."""
+    bs = 64
+    tdt = TDT[dtype]
+    lens = [300, 128, 65, 1024]
+    cached = [128, 64, 64, 512]
+    g = torch.Generator().manual_seed(9)
+    n = sum(lens)
+    q = torch.randn(n, h, d, generator=g).to(tdt).to(cuda_device)
+    k = torch.randn(n, kvh, d, generator=g).to(tdt).to(cuda_device)
+    v = torch.randn(n, kvh, d, generator=g).to(tdt).to(cuda_device)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    nblk = [(x + bs - 1) // bs for x in lens]
+    perm = torch.randperm(sum(nblk) + 5, generator=g)
+    kc = torch.full((perm.numel(), bs, kvh, d), float("nan"), dtype=tdt, device=cuda_device)
+    vc = torch.full((perm.numel(), bs, kvh, d), float("nan"), dtype=tdt, device=cuda_device)
+    bt = torch.full((len(lens), max(nblk)), -1, dtype=torch.int32)
+    slots, c0 = [], 0
+    for s, nb in enumerate(nblk):
+        bt[s, :nb] = perm[c0 : c0 + nb]
+        c0 += nb
+        slots += [int(bt[s, p // bs]) * bs + p % bs for p in range(lens[s])]
+    m.store_kvcache(k, v, kc, vc, torch.tensor(slots, dtype=torch.int32, device=cuda_device))
+    rows = np.concatenate([np.arange(cu[s] + cached[s], cu[s + 1]) for s in range(len(lens))])
+    lq = [l - c for l, c in zip(lens, cached)]
+    cu_q = torch.tensor(np.concatenate([[0], np.cumsum(lq)]).astype(np.int32), device=cuda_device)
+    cu_k = torch.tensor(cu, device=cuda_device)
+    scale = d**-0.5
+    out = m.prefill_varlen_attention(
+        q[torch.from_numpy(rows).to(cuda_device)], None, None, cu_q, cu_k, max(lq), max(lens), scale,
+        k_cache=kc, v_cache=vc, block_tables=bt.to(cuda_device),
+    )
+    full = orc.prefill_dense(_f32(q), _f32(k), _f32(v), cu, cu, scale)
+    err = np.abs(_f32(out) - full[rows])
+    assert np.isfinite(_f32(out)).all()
+    assert err.max() <= TOL[dtype], (m.ops.last_kernel(), err.max(), err.mean())
+
+
+# ---------------------------------------------------------------------------
+# the layer: Attention.forward through the Context, prefill then decode steps
+# ---------------------------------------------------------------------------
+
+
+@pytest.mark.parametrize("case", _cases("layer"))
+def test_attention_layer_flow_golden(m, cuda_device, case):
+    g = load_golden("layer")
+    dt = str(g[f"{case}.dtype"])
+    h, kvh, d, steps, _ = (int(x) for x in g[f"{case}.meta"])
+    scale = float(g[f"{case}.scale"])
+    attn = m.Attention(h, d, scale, kvh)
+    attn.k_cache = golden_to_torch(g[f"{case}.k_cache_in"], dt, cuda_device)
+    attn.v_cache = golden_to_torch(g[f"{case}.v_cache_in"], dt, cuda_device)
+    lens = np.diff(g[f"{case}.p.cu_seqlens"])
+    cu = torch.from_numpy(g[f"{case}.p.cu_seqlens"]).to(cuda_device)
+    m.set_context(
+        is_prefill=True, max_seqlen_q=int(lens.max()), max_seqlen_k=int(lens.max()),
+        cum_seqlens_q=cu, cum_seqlens_k=cu,
+        slot_mapping=torch.from_numpy(g[f"{case}.p.slots"]).to(cuda_device),
+        block_tables=torch.from_numpy(g[f"{case}.p.block_tables"]).to(cuda_device),
+    )
+    try:
+        out = attn(*(golden_to_torch(g[f"{case}.p.{x}"], dt, cuda_device) for x in "qkv"))
+    finally:
+        m.reset_context()
+    assert np.array_equal(_bits(attn.k_cache).ravel(), g[f"{case}.p.k_cache_out"].view(np.uint8).ravel())
+    assert np.array_equal(_bits(attn.v_cache).ravel(), g[f"{case}.p.v_cache_out"].view(np.uint8).ravel())
+    assert np.abs(_f32(out) - golden_to_float(g[f"{case}.p.out"], dt)).max() <= 2 * TOL[dt]
+    for st in range(steps):
+        pre = f"{case}.d{st}"
+        m.set_context(
+            is_prefill=False,
+            slot_mapping=torch.from_numpy(g[f"{pre}.slots"]).to(cuda_device),
+            context_lens=torch.from_numpy(g[f"{pre}.context_lens"]).to(cuda_device),
+            block_tables=torch.from_numpy(g[f"{pre}.block_tables"]).to(cuda_device),
+        )
+        try:
+            out = attn(*(golden_to_torch(g[f"{pre}.{x}"], dt, cuda_device) for x in "qkv"))
+        finally:
+            m.reset_context()
+        assert np.abs(_f32(out) - golden_to_float(g[f"{pre}.out"], dt)).max() <= TOL[dt]
+    assert np.array_equal(_bits(attn.k_cache).ravel(), g[f"{case}.k_cache_final"].view(np.uint8).ravel())
+    assert np.array_equal(_bits(attn.v_cache).ravel(), g[f"{case}.v_cache_final"].view(np.uint8).ravel())
+
+
+def test_attention_decode_before_cache_raises(m, cuda_device):
+    attn = m.Attention(4, 64, 0.0, 4)
+    assert abs(attn.scale - 64**-0.5) < 1e-12
+    m.set_context(is_prefill=False)
+    try:
+        with pytest.raises(RuntimeError, match="KV cache has not been initialized"):
+            attn(*(torch.zeros(1, 4, 64, device=cuda_device),) * 3)
+    finally:
+        m.reset_context()

@@ -155,3 +155,51 @@ def test_bf16_roundtrip_matches_torch():
     tb = x.to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
     assert np.array_equal(bits, tb)
     assert np.array_equal(orc.bf16_bits_to_f32(bits), x.to(torch.bfloat16).float().numpy())
+
+
+# ---------------------------------------------------------------------------
+# the torch-CPU port used for cpu_baseline timing: same golden vectors
+# ---------------------------------------------------------------------------
+from oracle import eager_port as port  # noqa: E402
+from tests.conftest import golden_to_torch  # noqa: E402
+
+
+@pytest.mark.parametrize("case", _cases(load_golden("store")))
+def test_eager_port_store(case):
+    import torch
+
+    g = load_golden("store")
+    dt = str(g[f"{case}.dtype"])
+    kc = golden_to_torch(g[f"{case}.k_cache_in"], dt).clone()
+    vc = golden_to_torch(g[f"{case}.v_cache_in"], dt).clone()
+    port.store_kvcache(golden_to_torch(g[f"{case}.key"], dt), golden_to_torch(g[f"{case}.value"], dt),
+                       kc, vc, torch.from_numpy(g[f"{case}.slots"]))
+    assert torch.equal(kc, golden_to_torch(g[f"{case}.k_cache_out"], dt))
+    assert torch.equal(vc, golden_to_torch(g[f"{case}.v_cache_out"], dt))
+
+
+@pytest.mark.parametrize("case", _cases(load_golden("decode")))
+def test_eager_port_decode(case):
+    import torch
+
+    g = load_golden("decode")
+    dt = str(g[f"{case}.dtype"])
+    out = port.paged_decode(
+        golden_to_torch(g[f"{case}.q"], dt), golden_to_torch(g[f"{case}.k_cache"], dt),
+        golden_to_torch(g[f"{case}.v_cache"], dt), torch.from_numpy(g[f"{case}.block_tables"]),
+        torch.from_numpy(g[f"{case}.context_lens"]), float(g[f"{case}.scale"]),
+    )
+    # same operators on the same inputs as the reference: identical up to thread-count reassociation
+    assert (out.float() - golden_to_torch(g[f"{case}.out"], dt).float()).abs().max().item() <= TOL[dt] / 4
+
+
+@pytest.mark.parametrize("case", _cases(load_golden("prefill")))
+def test_eager_port_prefill(case):
+    import torch
+
+    g = load_golden("prefill")
+    dt = str(g[f"{case}.dtype"])
+    cu = torch.from_numpy(g[f"{case}.cu_seqlens"])
+    out = port.prefill_dense(golden_to_torch(g[f"{case}.q"], dt), golden_to_torch(g[f"{case}.k"], dt),
+                             golden_to_torch(g[f"{case}.v"], dt), cu, cu, float(g[f"{case}.scale"]))
+    assert (out.float() - golden_to_torch(g[f"{case}.out"], dt).float()).abs().max().item() <= TOL[dt] / 4
