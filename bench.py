@@ -342,7 +342,7 @@ def run_b200(args, wl):
             "workload": wl["name"], "layers": L, "batch": B, "context": ctx, "q_heads_per_rank": H,
             "kv_heads_per_rank": KVH, "head_dim": D, "kvcache_block_size": BLOCK, "parallelism": f"tp{tp}",
             "num_kv_splits": splits, "cuda_graph": True,
-            "l2": f"inputs ({2 * bytes_layer_rank * L / 1e9:.1f} GB of KV per rank per step) are >> 126 MB L2; no flush needed",
+            "l2": f"inputs ({bytes_layer_rank * L / 1e9:.1f} GB of KV per rank per step) are >> 126 MB L2; no flush needed",
         },
         "tokens_per_s_attention_only": B / (ms_step * 1e-3),
         "roofline": {
