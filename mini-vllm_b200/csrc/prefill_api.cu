@@ -2,31 +2,10 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "prefill_args.h"
 
 namespace mvb200 {
 
-struct PrefillArgs {
-  const void* q;
-  int64_t q_row_stride;
-  const void* k;
-  const void* v;
-  int64_t k_row_stride, v_row_stride;
-  int64_t num_kv_rows;
-  const void* k_cache;
-  const void* v_cache;
-  const int32_t* block_tables;
-  int64_t bt_row_stride;
-  const int32_t* cu_q;
-  const int32_t* cu_k;
-  void* out;
-  int64_t out_row_stride;
-  int32_t num_seqs, total_q, max_seqlen_q, max_seqlen_k;
-  int32_t num_heads, num_kv_heads, head_dim, block_size;
-  int64_t num_blocks;
-  int32_t max_blocks;
-  float scale;
-  int32_t dtype;
-};
 
 int prefill_generic_dispatch(const void* q, int64_t q_row_stride, const void* k, const void* v,
                              int64_t k_row_stride, int64_t v_row_stride, const void* k_cache,
@@ -73,7 +52,7 @@ extern "C" int mvb200_prefill_varlen(
                 block_tables, bt_row_stride, cu_seqlens_q, cu_seqlens_k, out, out_row_stride,
                 num_seqs, total_q, max_seqlen_q, max_seqlen_k, num_heads, num_kv_heads, head_dim,
                 block_size, num_blocks, max_blocks_per_seq, scale, dtype};
-  static const bool force_generic = getenv("MVB200_PREFILL_GENERIC") != nullptr;
+  const bool force_generic = getenv("MVB200_PREFILL_GENERIC") != nullptr;  // debugging aid
   if (!force_generic) {
     const int rc = prefill_tcgen05_dispatch(a, s);
     if (rc >= 0) return rc;

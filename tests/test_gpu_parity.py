@@ -398,3 +398,141 @@ def test_attention_decode_before_cache_raises(m, cuda_device):
             attn(*(torch.zeros(1, 4, 64, device=cuda_device),) * 3)
     finally:
         m.reset_context()
+
+
+# ---------------------------------------------------------------------------
+# tcgen05 prefill kernel: selection, ragged shapes, BASELINE sizes
+# ---------------------------------------------------------------------------
+
+
+def _paged_prefill_problem(device, lens, cached, h, kvh, d, bs, dtype, seed, nan_fill=True):
+    """Full K/V for every sequence stored through block tables; queries are the uncached suffix."""
+    g = torch.Generator().manual_seed(seed)
+    n = sum(lens)
+    q = torch.randn(n, h, d, generator=g).to(dtype).to(device)
+    k = torch.randn(n, kvh, d, generator=g).to(dtype).to(device)
+    v = torch.randn(n, kvh, d, generator=g).to(dtype).to(device)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    nblk = [(x + bs - 1) // bs for x in lens]
+    perm = torch.randperm(sum(nblk) + 3, generator=g)
+    fill = float("nan") if nan_fill else 0.0
+    kc = torch.full((perm.numel(), bs, kvh, d), fill, dtype=dtype, device=device)
+    vc = torch.full((perm.numel(), bs, kvh, d), fill, dtype=dtype, device=device)
+    bt = torch.full((len(lens), max(max(nblk), 1)), -1, dtype=torch.int32)
+    slots, c0 = [], 0
+    for s, nb in enumerate(nblk):
+        bt[s, :nb] = perm[c0 : c0 + nb]
+        c0 += nb
+        slots += [int(bt[s, p // bs]) * bs + p % bs for p in range(lens[s])]
+    rows = np.concatenate([np.arange(cu[s] + cached[s], cu[s + 1]) for s in range(len(lens))]).astype(np.int64)
+    lq = [l - c for l, c in zip(lens, cached)]
+    cu_q = np.concatenate([[0], np.cumsum(lq)]).astype(np.int32)
+    return dict(q=q, k=k, v=v, cu=cu, cu_q=cu_q, rows=rows, lq=lq, kc=kc, vc=vc, bt=bt.to(device),
+                slots=torch.tensor(slots, dtype=torch.int32, device=device))
+
+
+def _oracle_rows(pr, seq, heads, h, kvh, scale):
+    """float64 oracle for one sequence and a few heads (keeps the CPU time bounded)."""
+    cu, group = pr["cu"], h // kvh
+    a, b = int(cu[seq]), int(cu[seq + 1])
+    outs = []
+    for hd in heads:
+        o = orc.prefill_dense(_f32(pr["q"][a:b, hd : hd + 1]), _f32(pr["k"][a:b, hd // group : hd // group + 1]),
+                              _f32(pr["v"][a:b, hd // group : hd // group + 1]), [0, b - a], [0, b - a], scale)
+        outs.append(o[:, 0])
+    return np.stack(outs, axis=1)  # [len, heads, D] for ALL positions of the sequence
+
+
+@pytest.mark.parametrize("bs", [64, 128, 256])
+@pytest.mark.parametrize("dtype", ["bf16", "f16"])
+def test_prefill_tcgen05_ragged_paged(m, cuda_device, bs, dtype):
+    """Lq/Lk off the 128/64 grid, a fully cached sequence (Lq = 0), single-token suffix,
+    never-written slots full of NaN, block sizes 64/128/256."""
+    h, kvh, d = 8, 2, 128
+    lens = [300, 2 * bs, 65, 1000, 129, 64]
+    cached = [0, 2 * bs, 64, 3 * bs if 3 * bs < 1000 else bs, 128, 0]
+    pr = _paged_prefill_problem(cuda_device, lens, cached, h, kvh, d, bs, TDT[dtype], 21)
+    m.store_kvcache(pr["k"], pr["v"], pr["kc"], pr["vc"], pr["slots"])
+    scale = d**-0.5
+    out = m.prefill_varlen_attention(
+        pr["q"][torch.from_numpy(pr["rows"]).to(cuda_device)], None, None,
+        torch.from_numpy(pr["cu_q"]).to(cuda_device), torch.from_numpy(pr["cu"]).to(cuda_device),
+        max(pr["lq"]), max(lens), scale, k_cache=pr["kc"], v_cache=pr["vc"], block_tables=pr["bt"],
+    )
+    assert m.ops.last_kernel() == "prefill_tcgen05"
+    full = orc.prefill_dense(_f32(pr["q"]), _f32(pr["k"]), _f32(pr["v"]), pr["cu"], pr["cu"], scale)
+    got = _f32(out)
+    assert np.isfinite(got).all()
+    err = np.abs(got - full[pr["rows"]])
+    assert err.max() <= TOL[dtype], (err.max(), err.mean())
+
+
+def test_prefill_tcgen05_dense_strided_source(m, cuda_device):
+    """No block tables (engine warm-up / layer tests): K/V are row-strided views of a fused qkv."""
+    h, kvh, d = 4, 2, 128
+    lens = [200, 1, 130, 64]
+    n = sum(lens)
+    g = torch.Generator().manual_seed(4)
+    fused = torch.randn(n, (h + 2 * kvh) * d, generator=g).to(torch.bfloat16).to(cuda_device)
+    q = fused[:, : h * d].view(n, h, d)
+    k = fused[:, h * d : (h + kvh) * d].view(n, kvh, d)
+    v = fused[:, (h + kvh) * d :].view(n, kvh, d)
+    cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
+    cut = torch.from_numpy(cu).to(cuda_device)
+    out = m.prefill_varlen_attention(q, k, v, cut, cut, max(lens), max(lens), d**-0.5)
+    assert m.ops.last_kernel() == "prefill_tcgen05"
+    ref = orc.prefill_dense(_f32(q), _f32(k), _f32(v), cu, cu, d**-0.5)
+    assert np.abs(_f32(out) - ref).max() <= TOL["bf16"]
+
+
+@pytest.mark.parametrize(
+    "name,lens,cached,h,kvh",
+    [
+        ("cfg3_8x(1024+1024)_tp1", [2048] * 8, [1024] * 8, 32, 8),
+        ("cfg3_1x(4096+4096)_tp1", [8192], [4096], 32, 8),
+        ("cfg3_tp8_rank", [2048] * 8, [1024] * 8, 4, 1),
+        ("cfg5_rank_16k_tokens", [1024] * 16, [0] * 16, 8, 1),
+    ],
+)
+def test_prefill_full_size_against_oracle_samples(m, cuda_device, name, lens, cached, h, kvh):
+    """BASELINE.json prefill sizes: 8k new tokens with 50 % prefix hits (cfg3), 16k tokens (cfg5)."""
+    d, bs = 128, 64
+    pr = _paged_prefill_problem(cuda_device, lens, cached, h, kvh, d, bs, torch.bfloat16, 33)
+    m.store_kvcache(pr["k"], pr["v"], pr["kc"], pr["vc"], pr["slots"])
+    scale = d**-0.5
+    out = m.prefill_varlen_attention(
+        pr["q"][torch.from_numpy(pr["rows"]).to(cuda_device)], None, None,
+        torch.from_numpy(pr["cu_q"]).to(cuda_device), torch.from_numpy(pr["cu"]).to(cuda_device),
+        max(pr["lq"]), max(lens), scale, k_cache=pr["kc"], v_cache=pr["vc"], block_tables=pr["bt"],
+    )
+    assert m.ops.last_kernel() == "prefill_tcgen05"
+    got = _f32(out)
+    assert np.isfinite(got).all()
+    heads = sorted({0, h // 2, h - 1})
+    worst = 0.0
+    for seq in sorted({0, len(lens) - 1}):
+        ref = _oracle_rows(pr, seq, heads, h, kvh, scale)  # all positions of the sequence
+        a = int(pr["cu_q"][seq])
+        mine = got[a : a + pr["lq"][seq]][:, heads]
+        err = np.abs(mine - ref[cached[seq] :])
+        worst = max(worst, float(err.max()))
+        assert err.max() <= TOL["bf16"], (name, seq, err.max(), err.mean())
+    # linearity in V (size-independent property): out(V) + out(V2) == out(V + V2) up to rounding
+    # is implied by the oracle check on sampled rows; here check row-sums of P == 1 via V = ones
+    ones = torch.ones_like(pr["vc"])
+    out1 = m.prefill_varlen_attention(
+        pr["q"][torch.from_numpy(pr["rows"]).to(cuda_device)], None, None,
+        torch.from_numpy(pr["cu_q"]).to(cuda_device), torch.from_numpy(pr["cu"]).to(cuda_device),
+        max(pr["lq"]), max(lens), scale, k_cache=pr["kc"], v_cache=ones, block_tables=pr["bt"],
+    )
+    assert (out1.float() - 1.0).abs().max().item() <= 1e-2
+
+
+def test_prefill_kernel_selection(m, cuda_device):
+    """bf16/fp16 with head_dim 128 -> tcgen05; everything else -> the generic kernel."""
+    for dt, d, want in [(torch.bfloat16, 128, "prefill_tcgen05"), (torch.float16, 128, "prefill_tcgen05"),
+                        (torch.float32, 128, "prefill_generic"), (torch.bfloat16, 64, "prefill_generic")]:
+        q = torch.randn(10, 2, d, device=cuda_device).to(dt)
+        cu = torch.tensor([0, 10], dtype=torch.int32, device=cuda_device)
+        m.prefill_varlen_attention(q, q, q, cu, cu, 10, 10, 0.1)
+        assert m.ops.last_kernel() == want
