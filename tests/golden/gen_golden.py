@@ -369,9 +369,97 @@ def gen_layer():
     save("layer", **out)
 
 
+# ---------------------------------------------------------------------------
+# attention metadata: the reference's own Sequence + BlockManager + executor prep
+# ---------------------------------------------------------------------------
+
+
+def gen_metadata():
+    import types
+
+    from minivllm.engine.block_manager import BlockManager
+    from minivllm.engine.inference_executor import InferenceExecutor
+    from minivllm.engine.sequence import Sequence
+    from minivllm.utils.context import get_context
+
+    bs, max_seqs, max_model_len = 64, 8, 1024
+    fake = types.SimpleNamespace(block_size=bs, device=torch.device("cpu"))
+    fake.config = types.SimpleNamespace(max_num_seqs=max_seqs, max_model_len=max_model_len, kvcache_block_size=bs)
+    for name in ("_list_to_device_tensor", "_prepare_block_tables", "_prepare_block_tables_decode"):
+        setattr(fake, name, types.MethodType(getattr(InferenceExecutor, name), fake))
+    mb = (max_model_len + bs - 1) // bs
+    fake._decode_input_ids_cpu = torch.zeros(max_seqs, dtype=torch.long)
+    fake._decode_positions_cpu = torch.zeros(max_seqs, dtype=torch.long)
+    fake._decode_slot_mapping_cpu = torch.zeros(max_seqs, dtype=torch.int32)
+    fake._decode_context_lens_cpu = torch.zeros(max_seqs, dtype=torch.int32)
+    fake._decode_input_ids = torch.zeros(max_seqs, dtype=torch.long)
+    fake._decode_positions = torch.zeros(max_seqs, dtype=torch.long)
+    fake._decode_slot_mapping = torch.zeros(max_seqs, dtype=torch.int32)
+    fake._decode_context_lens = torch.zeros(max_seqs, dtype=torch.int32)
+    fake._decode_block_tables_cpu = torch.full((max_seqs, mb), -1, dtype=torch.int32)
+    fake._decode_block_tables = torch.full((max_seqs, mb), -1, dtype=torch.int32)
+    fake._max_blocks_per_seq = mb
+
+    g = torch.Generator().manual_seed(500)
+    rnd = lambda n: torch.randint(10, 30000, (n,), generator=g).tolist()  # noqa: E731
+    bm = BlockManager(40, bs)
+    out = {}
+    steps = []
+
+    def record(tag, seqs, prefill):
+        if prefill:
+            ids, pos = InferenceExecutor._prepare_prefill_input(fake, seqs)
+        else:
+            ids, pos = InferenceExecutor._prepare_decode_input(fake, seqs)
+        ctx = get_context()
+        out[f"{tag}.n"] = np.array(len(seqs))
+        for i, s in enumerate(seqs):
+            out[f"{tag}.seq{i}.token_ids"] = np.array(s.token_ids, dtype=np.int64)
+            out[f"{tag}.seq{i}.block_table"] = np.array(s.block_table, dtype=np.int64)
+            out[f"{tag}.seq{i}.num_cached"] = np.array(s.num_cached_tokens)
+        out[f"{tag}.input_ids"] = to_np(ids)
+        out[f"{tag}.positions"] = to_np(pos)
+        out[f"{tag}.is_prefill"] = np.array(int(prefill))
+        for f in ("cum_seqlens_q", "cum_seqlens_k", "slot_mapping", "context_lens", "block_tables"):
+            v = getattr(ctx, f)
+            if v is not None:
+                out[f"{tag}.{f}"] = to_np(v.clone())
+        out[f"{tag}.max_seqlen_q"] = np.array(ctx.max_seqlen_q)
+        out[f"{tag}.max_seqlen_k"] = np.array(ctx.max_seqlen_k)
+        steps.append(tag)
+        reset_context()
+
+    base = rnd(254)
+    a = Sequence(base, block_size=bs)
+    bm.allocate(a)
+    record("p0", [a], True)
+    b = Sequence(base[:128] + rnd(70), block_size=bs)   # two full blocks hit the prefix cache
+    c = Sequence(rnd(64), block_size=bs)                # exactly one block
+    d = Sequence(base[:192], block_size=bs)             # fully cached prompt: Lq = 0 (block_manager.py:324-327)
+    for s in (b, c, d):
+        bm.allocate(s)
+    assert b.num_cached_tokens == 128 and d.num_cached_tokens == 192
+    record("p1", [b, c, d], True)
+    live = [a, b, c]
+    for t in range(4):  # a: 255, 256 (hash sealed), 257 (new block), 258; c: 65 (new block) ...
+        for s in live:
+            s.append_token(int(torch.randint(10, 30000, (1,), generator=g)))
+            bm.may_append(s)
+        record(f"d{t}", live, False)
+    # warm-up shaped batches: no block tables at all (inference_executor.py:390-407)
+    w = [Sequence([0] * 16, block_size=bs) for _ in range(2)]
+    record("w_prefill", w, True)
+    for s in w:
+        s.append_token(0)
+    record("w_decode", w, False)
+    out["steps"] = np.array(steps)
+    save("metadata", **out)
+
+
 if __name__ == "__main__":
     print("generating golden vectors from", REFERENCE)
     gen_store()
     gen_decode()
     gen_prefill()
     gen_layer()
+    gen_metadata()
