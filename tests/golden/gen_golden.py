@@ -456,6 +456,75 @@ def gen_metadata():
     save("metadata", **out)
 
 
+# ---------------------------------------------------------------------------
+# end to end: the reference's LLM.generate on CPU (fp32, eager, random-init tiny Qwen3 / Qwen2)
+# ---------------------------------------------------------------------------
+
+
+def gen_engine():
+    import json
+    import tempfile
+    from unittest import mock
+
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from harness.model import PRESETS, seeded_tensor
+
+    import minivllm.models.manager as manager
+    from minivllm import LLM, SamplingParams
+    from minivllm.config import Config
+
+    def seeded_load(model, path):  # stands in for the safetensors loader (utils/loader.py:90-239)
+        with torch.no_grad():
+            for name, param in model.named_parameters():
+                param.copy_(seeded_tensor(name, tuple(param.shape)).to(param.dtype))
+
+    class Tok:  # manager.py:97-106, llm_engine.py:107-108,359-361
+        eos_token_id = 1
+        pad_token = "<pad>"
+        pad_token_id = 0
+
+        def batch_decode(self, ids, **kw):
+            return ["" for _ in ids]
+
+        def decode(self, ids, **kw):
+            return ""
+
+    out = {}
+    names = []
+    for preset, arch, mtype in (("tiny-qwen3", "Qwen3ForCausalLM", "qwen3"), ("tiny-qwen2", "Qwen2ForCausalLM", "qwen2")):
+        cfg = PRESETS[preset]
+        tmp = tempfile.mkdtemp()
+        json.dump({
+            "architectures": [arch], "model_type": mtype, "hidden_size": cfg.hidden_size,
+            "num_hidden_layers": cfg.num_layers, "num_attention_heads": cfg.num_heads,
+            "num_key_value_heads": cfg.num_kv_heads, "head_dim": cfg.head_dim,
+            "intermediate_size": cfg.intermediate_size, "vocab_size": cfg.vocab_size,
+            "rms_norm_eps": cfg.rms_eps, "rope_theta": cfg.rope_theta,
+            "max_position_embeddings": cfg.max_position, "tie_word_embeddings": cfg.tie_embeddings,
+            "hidden_act": "silu", "attention_bias": cfg.qkv_bias, "torch_dtype": "float32",
+        }, open(os.path.join(tmp, "config.json"), "w"))
+        g = torch.Generator().manual_seed(600)
+        # distinct prompts, ONE call: the reference's eager prefill mis-slices k/v as soon as any
+        # sequence in the batch has a prefix hit, so hits are kept out of the
+        # golden run; prefix-hit generation is checked by self-consistency in tests/test_harness.py.
+        lens = [165, 13, 203, 64, 250]  # 250 crosses a block boundary while decoding
+        prompts = [torch.randint(10, cfg.vocab_size - 10, (n,), generator=g).tolist() for n in lens]
+        with mock.patch.object(manager, "load_model", seeded_load), \
+                mock.patch.object(manager.AutoTokenizer, "from_pretrained", lambda *a, **k: Tok()):
+            llm = LLM(Config(model=tmp, max_num_seqs=8, max_model_len=1024, enforce_eager=True, dtype="float32",
+                             num_kvcache_blocks=64))
+            res = llm.generate(prompts, SamplingParams(temperature=0.0, max_tokens=32, ignore_eos=True), use_tqdm=False)
+            assert llm.scheduler.block_manager.stats["cache_hits"] == 0
+        out[f"{preset}.n"] = np.array(len(prompts))
+        for i, (p, r) in enumerate(zip(prompts, res)):
+            out[f"{preset}.prompt{i}"] = np.array(p, dtype=np.int64)
+            out[f"{preset}.tokens{i}"] = np.array(r["token_ids"], dtype=np.int64)
+        names.append(preset)
+        print("   ", preset, [r["token_ids"][:6] for r in res])
+    out["presets"] = np.array(names)
+    save("engine", **out)
+
+
 if __name__ == "__main__":
     print("generating golden vectors from", REFERENCE)
     gen_store()
@@ -463,3 +532,4 @@ if __name__ == "__main__":
     gen_prefill()
     gen_layer()
     gen_metadata()
+    gen_engine()
