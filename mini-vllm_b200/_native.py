@@ -12,7 +12,8 @@ import os
 from ctypes import c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmvb200.so")
+# MVB200_LIB points debugging tools at an instrumented build of the same sources (tools/prefill_trace.py)
+LIB_PATH = os.environ.get("MVB200_LIB") or os.path.join(_HERE, "libmvb200.so")
 
 _lib = None
 

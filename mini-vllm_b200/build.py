@@ -43,11 +43,19 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile every .cu for sm_100a and link the shared library.  Returns its path."""
+def build(force: bool = False, verbose: bool = False, trace: bool = False) -> str:
+    """Compile every .cu for sm_100a and link the shared library.  Returns its path.
+
+    ``trace=True`` builds libmvb200_trace.so from the same sources with -DPF_TRACE (the prefill kernel
+    records a per-tile clock64 timeline; used by tools/prefill_trace.py, never by the product path)."""
+    if trace:
+        return _build(os.path.join(HERE, "libmvb200_trace.so"), os.path.join(HERE, "build_trace"), ["-DPF_TRACE"], verbose)
     if not force and not needs_build():
         return LIB
-    objdir = os.path.join(HERE, "build")
+    return _build(LIB, os.path.join(HERE, "build"), [], verbose)
+
+
+def _build(LIB: str, objdir: str, extra: list, verbose: bool) -> str:
     os.makedirs(objdir, exist_ok=True)
     nvcc = _nvcc()
     procs = []
@@ -55,7 +63,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for src in SOURCES:
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
@@ -77,4 +85,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, trace="--trace" in sys.argv))

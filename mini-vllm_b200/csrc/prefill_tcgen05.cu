@@ -19,6 +19,7 @@
 // thread arrivals); no __syncthreads in the main loop.
 // Tensor-bound: 4*D flops per unmasked (q,k) pair per head.
 #include <math.h>
+#include <stdlib.h>
 
 #include <type_traits>
 
@@ -29,6 +30,28 @@ namespace mvb200 {
 
 
 namespace pf {
+
+// Pipeline trace (debug builds only, -DPF_TRACE; see tools/prefill_trace.py): one CTA records clock64
+// at every hand-off of its three roles so stalls can be attributed without guessing.
+#ifdef PF_TRACE
+__device__ unsigned long long g_trace[3 * 64 * 8];
+__device__ unsigned long long g_cta[8192 * 4];  // per CTA: smid | n_kt << 32, t_start, t_first_S, t_end (globaltimer ns)
+MVB_DEV unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)::"memory");
+  return t;
+}
+#define PF_T(role, j, ev)                                                                     \
+  do {                                                                                        \
+    if (traced && (j) < 64) {                                                                 \
+      unsigned long long t_;                                                                  \
+      asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_)::"memory");                            \
+      g_trace[((role) * 64 + (j)) * 8 + (ev)] = t_;                                           \
+    }                                                                                         \
+  } while (0)
+#else
+#define PF_T(role, j, ev) do {} while (0)
+#endif
 
 constexpr int kD = 128;
 constexpr int kBM = 128;               // query rows per CTA
@@ -41,7 +64,53 @@ constexpr int kKVHalfBytes = kBN * 128;  // [64 rows][128 B]
 constexpr int kKVBytes = 2 * kKVHalfBytes;
 constexpr int kTmemCols = 256;
 constexpr int kColS = 0, kColO = 128;
+constexpr int kDefaultEmu = 16;
 constexpr float kRescaleThreshold = 8.f;  // log2 domain: rescale O only when the max grew by > 2^8
+
+// ---- packed fp32x2 arithmetic (Blackwell FFMA2/FADD2: two lanes per issue slot) ----
+MVB_DEV uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+MVB_DEV void unpack2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+MVB_DEV uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+MVB_DEV uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+MVB_DEV float ex2_mufu(float x) {  // MUFU.EX2, flush-to-zero: no denormal fix-up code around it
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// 2^x for a pair on the FMA pipe (relieves the MUFU unit, which otherwise ties with the tensor pipe):
+// round-to-nearest split x = n + f, f in [-0.5, 0.5], degree-3 minimax polynomial for 2^f (max rel.
+// error 7.5e-5, far inside bf16's 2^-9), exponent add on the integer pipe.  x is clamped to >= -126.
+MVB_DEV void ex2_poly2(uint64_t x, float& y0, float& y1) {
+  float x0, x1;
+  unpack2(x, x0, x1);
+  x = pack2(fmaxf(x0, -126.f), fmaxf(x1, -126.f));
+  const uint64_t magic = pack2(12582912.f, 12582912.f);          // 1.5 * 2^23
+  const uint64_t t = add2(x, magic);                              // integer part lands in the low mantissa bits
+  const uint64_t n = add2(t, pack2(-12582912.f, -12582912.f));
+  const uint64_t f = fma2(n, pack2(-1.f, -1.f), x);               // x - n
+  uint64_t p = fma2(pack2(0.05517141f, 0.05517141f), f, pack2(0.24261075f, 0.24261075f));
+  p = fma2(p, f, pack2(0.69326097f, 0.69326097f));
+  p = fma2(p, f, pack2(0.99992812f, 0.99992812f));
+  float p0, p1, t0, t1;
+  unpack2(p, p0, p1);
+  unpack2(t, t0, t1);
+  y0 = __int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23));
+  y1 = __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23));
+}
 
 // barrier slots
 enum {
@@ -71,7 +140,7 @@ struct Params {
   float scale_log2;
 };
 
-template <typename T>
+template <typename T, int kEmu>
 __global__ void __launch_bounds__(kThreads, 2)
 prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
                        const __grid_constant__ CUtensorMap tmap_k,
@@ -101,6 +170,17 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const int n_kt = kv_end > 0 ? (kv_end + kBN - 1) / kBN : 0;
   const int kvh = head / (p.num_heads / p.num_kv_heads);
   T* out = reinterpret_cast<T*>(p.out);
+#ifdef PF_TRACE
+  const int cta_lin = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+  if (threadIdx.x == 64 && cta_lin < 8192) {
+    uint32_t smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_cta[cta_lin * 4 + 0] = (unsigned long long)smid | ((unsigned long long)n_kt << 32);
+    g_cta[cta_lin * 4 + 1] = gtime();
+  }
+  const bool traced = blockIdx.x == 0 && blockIdx.y == gridDim.y / 2 && blockIdx.z == gridDim.z / 2 && lane == 0 &&
+                      (warp <= 2);
+#endif
 
   if (n_kt == 0) {  // Lk < Lq corner: rows that see no key produce zeros
     for (int i = threadIdx.x; i < rows * kD; i += blockDim.x)
@@ -132,28 +212,34 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
-    if (lane == 0) {
+    // The whole warp runs the loop (uniform control flow); one elected lane issues.
+    if (elect_one()) {
       tma_prefetch_desc(&tmap_q);
       tma_prefetch_desc(&tmap_k);
       tma_prefetch_desc(&tmap_v);
       mbar_arrive_expect_tx(bar(BAR_Q_FULL), kQBytes);
       tma_load_3d(sQ, &tmap_q, bar(BAR_Q_FULL), 0, head, q0 + row0);
       tma_load_3d(sQ + kQHalfBytes, &tmap_q, bar(BAR_Q_FULL), 64, head, q0 + row0);
-      const int32_t* bt = p.block_tables + (int64_t)seq * p.bt_row_stride;
-      auto page_of = [&](int j) -> int {
-        const int v = __ldg(bt + min(j / p.tiles_per_block, p.max_blocks - 1));
-        return (v >= 0 && v < p.num_blocks) ? v : p.num_blocks;  // invalid -> OOB -> zero tile
-      };
-      int bid_next = p.paged ? page_of(0) : 0;
-      for (int j = 0; j < n_kt; ++j) {
-        const int s = j % kKVStages;
-        const uint32_t ph = (j / kKVStages) & 1;
-        const int bid = bid_next;
-        if (p.paged && j + 1 < n_kt) bid_next = page_of(j + 1);
-        const int sub = p.paged ? (j % p.tiles_per_block) * kBN : 0;
-        mbar_wait(bar(BAR_K_EMPTY + s), ph ^ 1);
+    }
+    __syncwarp();
+    const int32_t* bt = p.block_tables + (int64_t)seq * p.bt_row_stride;
+    auto page_of = [&](int j) -> int {
+      const int v = __ldg(bt + min(j / p.tiles_per_block, p.max_blocks - 1));
+      return (v >= 0 && v < p.num_blocks) ? v : p.num_blocks;  // invalid -> OOB -> zero tile
+    };
+    int bid_next = p.paged ? page_of(0) : 0;
+    for (int j = 0; j < n_kt; ++j) {
+      const int s = j % kKVStages;
+      const uint32_t ph = (j / kKVStages) & 1;
+      const int bid = bid_next;
+      if (p.paged && j + 1 < n_kt) bid_next = page_of(j + 1);
+      const int sub = p.paged ? (j % p.tiles_per_block) * kBN : 0;
+      PF_T(0, j, 0);
+      mbar_wait(bar(BAR_K_EMPTY + s), ph ^ 1);
+      PF_T(0, j, 1);
+      const uint32_t kd = sK + s * kKVBytes;
+      if (elect_one()) {
         mbar_arrive_expect_tx(bar(BAR_K_FULL + s), kKVBytes);
-        const uint32_t kd = sK + s * kKVBytes;
         if (p.paged) {
           tma_load_4d(kd, &tmap_k, bar(BAR_K_FULL + s), 0, kvh, sub, bid);
           tma_load_4d(kd + kKVHalfBytes, &tmap_k, bar(BAR_K_FULL + s), 64, kvh, sub, bid);
@@ -161,9 +247,13 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
           tma_load_3d(kd, &tmap_k, bar(BAR_K_FULL + s), 0, kvh, k0 + j * kBN);
           tma_load_3d(kd + kKVHalfBytes, &tmap_k, bar(BAR_K_FULL + s), 64, kvh, k0 + j * kBN);
         }
-        mbar_wait(bar(BAR_V_EMPTY + s), ph ^ 1);
+      }
+      __syncwarp();
+      mbar_wait(bar(BAR_V_EMPTY + s), ph ^ 1);
+      PF_T(0, j, 2);
+      const uint32_t vd = sV + s * kKVBytes;
+      if (elect_one()) {
         mbar_arrive_expect_tx(bar(BAR_V_FULL + s), kKVBytes);
-        const uint32_t vd = sV + s * kKVBytes;
         if (p.paged) {
           tma_load_4d(vd, &tmap_v, bar(BAR_V_FULL + s), 0, kvh, sub, bid);
           tma_load_4d(vd + kKVHalfBytes, &tmap_v, bar(BAR_V_FULL + s), 64, kvh, sub, bid);
@@ -172,47 +262,71 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
           tma_load_3d(vd + kKVHalfBytes, &tmap_v, bar(BAR_V_FULL + s), 64, kvh, k0 + j * kBN);
         }
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
-      constexpr uint32_t idesc_qk = umma_idesc(kBM, kBN, kBf16, false, false);
-      constexpr uint32_t idesc_pv = umma_idesc(kBM, kD, kBf16, false, true);
-      const int last_valid = kv_end - (n_kt - 1) * kBN;  // keys in the last tile that exist
-      auto issue_pv = [&](int i) {
-        const int b = i & 1, s = i % kKVStages;
-        mbar_wait(bar(BAR_V_FULL + s), (i / kKVStages) & 1);
-        mbar_wait(bar(BAR_P_FULL + b), (i >> 1) & 1);
-        tc_fence_after();
-        const uint32_t vb = sV + s * kKVBytes;
-        // skip 16-key groups that lie entirely past the last needed key
-        const int ksteps = (i == n_kt - 1) ? (last_valid + 15) / 16 : kBN / 16;
-        for (int kk = 0; kk < ksteps; ++kk) {
-          const uint64_t b_desc = umma_smem_desc(vb + kk * 16 * 128, kKVHalfBytes, 1024);
-          umma_ts(tmem + kColO, tmem + kColS + b * kBN + kk * 8, b_desc, idesc_pv, (i > 0 || kk > 0) ? 1u : 0u);
+    // Warp-uniform loop, one elected lane issues; descriptors advance by adding to their low word.
+    constexpr uint32_t idesc_qk = umma_idesc(kBM, kBN, kBf16, false, false);
+    constexpr uint32_t idesc_pv = umma_idesc(kBM, kD, kBf16, false, true);
+    constexpr uint32_t hi_kmajor = umma_desc_hi(1024);  // Q, K: K-major, 8-row groups 1 KiB apart
+    constexpr uint32_t hi_v = umma_desc_hi(1024);       // V: MN-major, 8-key groups 1 KiB apart
+    const uint32_t q_lo = umma_desc_lo(sQ, 16);
+    const uint32_t k_lo0 = umma_desc_lo(sK, 16);
+    const uint32_t v_lo0 = umma_desc_lo(sV, kKVHalfBytes);  // LBO = distance between the 64-column halves
+    const int last_valid = kv_end - (n_kt - 1) * kBN;  // keys in the last tile that exist
+    auto issue_pv = [&](int i) {
+      const int b = i & 1, s = i % kKVStages;
+      mbar_wait(bar(BAR_V_FULL + s), (i / kKVStages) & 1);
+      PF_T(1, i, 4);
+      mbar_wait(bar(BAR_P_FULL + b), (i >> 1) & 1);
+      PF_T(1, i, 5);
+      tc_fence_after();
+      // skip 16-key groups that lie entirely past the last needed key
+      const int ksteps = (i == n_kt - 1) ? (last_valid + 15) / 16 : kBN / 16;
+      if (elect_one()) {
+        const uint32_t v_lo = v_lo0 + s * (kKVBytes >> 4);
+        const uint32_t p_col = tmem + kColS + b * kBN;
+#pragma unroll
+        for (int kk = 0; kk < kBN / 16; ++kk) {
+          if (kk < ksteps)
+            umma_ts(tmem + kColO, p_col + kk * 8, umma_desc(hi_v, v_lo + kk * (16 * 128 >> 4)), idesc_pv,
+                    (i > 0 || kk > 0) ? 1u : 0u);
         }
         umma_commit(bar(BAR_V_EMPTY + s));
         umma_commit(bar(BAR_PV_DONE + b));
-      };
-      mbar_wait(bar(BAR_Q_FULL), 0);
-      for (int j = 0; j < n_kt; ++j) {
-        const int b = j & 1, s = j % kKVStages;
-        mbar_wait(bar(BAR_K_FULL + s), (j / kKVStages) & 1);
-        if (j >= 2) mbar_wait(bar(BAR_PV_DONE + b), ((j - 2) >> 1) & 1);  // S/P buffer b is free again
-        tc_fence_after();
-        const uint32_t kb = sK + s * kKVBytes;
+      }
+      __syncwarp();
+      PF_T(1, i, 6);
+    };
+    mbar_wait(bar(BAR_Q_FULL), 0);
+    for (int j = 0; j < n_kt; ++j) {
+      const int b = j & 1, s = j % kKVStages;
+      PF_T(1, j, 0);
+      mbar_wait(bar(BAR_K_FULL + s), (j / kKVStages) & 1);
+      PF_T(1, j, 1);
+      if (j >= 2) mbar_wait(bar(BAR_PV_DONE + b), ((j - 2) >> 1) & 1);  // S/P buffer b is free again
+      PF_T(1, j, 2);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t k_lo = k_lo0 + s * (kKVBytes >> 4);
+        const uint32_t s_col = tmem + kColS + b * kBN;
 #pragma unroll
         for (int kk = 0; kk < kD / 16; ++kk) {
-          const uint64_t a_desc = umma_smem_desc(sQ + (kk >> 2) * kQHalfBytes + (kk & 3) * 32, 16, 1024);
-          const uint64_t b_desc = umma_smem_desc(kb + (kk >> 2) * kKVHalfBytes + (kk & 3) * 32, 16, 1024);
-          umma_ss(tmem + kColS + b * kBN, a_desc, b_desc, idesc_qk, kk > 0 ? 1u : 0u);
+          // 16 elements = 32 B inside the 128-B swizzle row; the next 64 elements are the next half-tile
+          const uint32_t qoff = ((kk >> 2) * kQHalfBytes + (kk & 3) * 32) >> 4;
+          const uint32_t koff = ((kk >> 2) * kKVHalfBytes + (kk & 3) * 32) >> 4;
+          umma_ss(s_col, umma_desc(hi_kmajor, q_lo + qoff), umma_desc(hi_kmajor, k_lo + koff), idesc_qk,
+                  kk > 0 ? 1u : 0u);
         }
         umma_commit(bar(BAR_K_EMPTY + s));
         umma_commit(bar(BAR_S_FULL + b));
-        if (j >= 1) issue_pv(j - 1);
       }
-      issue_pv(n_kt - 1);
+      __syncwarp();
+      PF_T(1, j, 3);
+      if (j >= 1) issue_pv(j - 1);
     }
+    issue_pv(n_kt - 1);
   } else {
     // =========================== softmax warpgroup ===========================
     const int quarter = warp & 3;                 // TMEM lanes this warp may touch
@@ -223,19 +337,25 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
 
     for (int j = 0; j < n_kt; ++j) {
       const int b = j & 1;
+      PF_T(2, j, 0);
       mbar_wait(bar(BAR_S_FULL + b), (j >> 1) & 1);
+      PF_T(2, j, 1);
+#ifdef PF_TRACE
+      if (j == 0 && threadIdx.x == 64 && cta_lin < 8192) g_cta[cta_lin * 4 + 2] = gtime();
+#endif
       tc_fence_after();
       float s[kBN];
       {
-        uint32_t raw[32];
-        tmem_ld32(lane_base + kColS + b * kBN, raw);
+        uint32_t raw0[32], raw1[32];
+        tmem_ld32(lane_base + kColS + b * kBN, raw0);
+        tmem_ld32(lane_base + kColS + b * kBN + 32, raw1);
         tmem_wait_ld();
+        PF_T(2, j, 2);
 #pragma unroll
-        for (int c = 0; c < 32; ++c) s[c] = __uint_as_float(raw[c]);
-        tmem_ld32(lane_base + kColS + b * kBN + 32, raw);
-        tmem_wait_ld();
-#pragma unroll
-        for (int c = 0; c < 32; ++c) s[32 + c] = __uint_as_float(raw[c]);
+        for (int c = 0; c < 32; ++c) {
+          s[c] = __uint_as_float(raw0[c]);
+          s[32 + c] = __uint_as_float(raw1[c]);
+        }
       }
       const int col0 = j * kBN;
       if (col0 + kBN - 1 > shift + row0) {  // tile touches the diagonal (CTA-uniform test)
@@ -243,16 +363,16 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
 #pragma unroll
         for (int c = 0; c < kBN; ++c) s[c] = c <= lim ? s[c] : -INFINITY;
       }
-      float mx = s[0];
+      float mx = fmaxf(s[0], s[1]);
 #pragma unroll
-      for (int c = 1; c < kBN; ++c) mx = fmaxf(mx, s[c]);
+      for (int c = 2; c < kBN; c += 2) mx = fmaxf(mx, fmaxf(s[c], s[c + 1]));
       mx *= p.scale_log2;
       // lazy rescale: keep exponentiating against m_ref until the true max outruns it by 2^8
       const bool grow = mx > m_ref + kRescaleThreshold;
       if (__any_sync(0xffffffffu, grow)) {
         const float m_new = grow ? mx : m_ref;
         if (j > 0) {
-          const float sc = exp2f(m_ref - m_new);  // 1 for lanes that keep their reference
+          const float sc = ex2_mufu(m_ref - m_new);  // 1 for lanes that keep their reference
           l_run *= sc;
           mbar_wait(bar(BAR_PV_DONE + ((j - 1) & 1)), ((j - 1) >> 1) & 1);  // O is quiescent
           tc_fence_after();
@@ -269,18 +389,35 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
         m_ref = m_new;
       }
       const float m_use = m_ref == -INFINITY ? 0.f : m_ref;
+      PF_T(2, j, 3);
       uint32_t pk[kBN / 2];
-      float sum = 0.f;
+      const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
+      const uint64_t negm2 = pack2(-m_use, -m_use);
+      uint64_t sum2 = pack2(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < kBN; c += 2) {
-        const float p0 = exp2f(s[c] * p.scale_log2 - m_use);
-        const float p1 = exp2f(s[c + 1] * p.scale_log2 - m_use);
-        sum += p0 + p1;
+        const uint64_t x = fma2(pack2(s[c], s[c + 1]), scale2, negm2);
+        float p0, p1;
+        // kEmu of every 64 columns take the FMA-pipe exponential, interleaved with the MUFU ones
+        if (kEmu > 0 && ((c / 2) * (kEmu / 2)) % (kBN / 2) < kEmu / 2) {
+          ex2_poly2(x, p0, p1);
+        } else {
+          float x0, x1;
+          unpack2(x, x0, x1);
+          p0 = ex2_mufu(x0);
+          p1 = ex2_mufu(x1);
+        }
+        sum2 = add2(sum2, pack2(p0, p1));
         pk[c / 2] = Mma16816<T>::pack(p0, p1);
       }
+      float sum, sum_hi;
+      unpack2(sum2, sum, sum_hi);
+      sum += sum_hi;
       l_run += sum;
+      PF_T(2, j, 4);
       tmem_st32(lane_base + kColS + b * kBN, pk);  // P overwrites the first half of S_b
       tmem_wait_st();
+      PF_T(2, j, 5);
 
       if (j == n_kt - 1 && warp == 2) {
         // keys >= kv_end in the last tile were never written: their V rows may hold NaN/Inf bit
@@ -302,6 +439,7 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(BAR_P_FULL + b));
+      PF_T(2, j, 6);
     }
 
     // ---- epilogue: O / l -> global ----
@@ -331,9 +469,12 @@ prefill_tcgen05_kernel(const __grid_constant__ CUtensorMap tmap_q,
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem, kTmemCols);
+#ifdef PF_TRACE
+  if (threadIdx.x == 64 && cta_lin < 8192) g_cta[cta_lin * 4 + 3] = gtime();
+#endif
 }
 
-template <typename T>
+template <typename T, int kEmu>
 static int launch(const PrefillArgs& a, cudaStream_t stream) {
   CUtensorMap mq, mk, mv;
   {
@@ -380,7 +521,7 @@ static int launch(const PrefillArgs& a, cudaStream_t stream) {
   p.scale_log2 = a.scale * kLog2e;
 
   constexpr int smem = kQBytes + 2 * kKVStages * kKVBytes + 8 * BAR_COUNT + 16 + 1024;
-  auto kern = prefill_tcgen05_kernel<T>;
+  auto kern = prefill_tcgen05_kernel<T, kEmu>;
   static thread_local bool configured = false;
   if (!configured) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
@@ -413,8 +554,29 @@ int prefill_tcgen05_dispatch(const PrefillArgs& a, cudaStream_t stream) {
       return -1;
   }
   note_kernel("prefill_tcgen05");
-  return a.dtype == MVB200_BF16 ? pf::launch<__nv_bfloat16>(a, stream)
-                                : pf::launch<__half>(a, stream);
+  // Columns (of every 64) whose exponential runs on the FMA pipe instead of MUFU.  Tuning knob for
+  // profiling only (MVB200_PREFILL_EMU = 0 | 8 | 16 | 24); the default is the measured optimum.
+  static const int emu = [] {
+    const char* e = getenv("MVB200_PREFILL_EMU");
+    const int v = e ? atoi(e) : pf::kDefaultEmu;
+    return (v == 0 || v == 8 || v == 16 || v == 24) ? v : pf::kDefaultEmu;
+  }();
+  const bool bf = a.dtype == MVB200_BF16;
+  switch (emu) {
+    case 0: return bf ? pf::launch<__nv_bfloat16, 0>(a, stream) : pf::launch<__half, 0>(a, stream);
+    case 8: return bf ? pf::launch<__nv_bfloat16, 8>(a, stream) : pf::launch<__half, 8>(a, stream);
+    case 24: return bf ? pf::launch<__nv_bfloat16, 24>(a, stream) : pf::launch<__half, 24>(a, stream);
+    default: return bf ? pf::launch<__nv_bfloat16, 16>(a, stream) : pf::launch<__half, 16>(a, stream);
+  }
 }
 
 }  // namespace mvb200
+
+#ifdef PF_TRACE
+extern "C" __attribute__((visibility("default"))) int mvb200_debug_read_prefill_trace(unsigned long long* dst) {
+  return (int)cudaMemcpyFromSymbol(dst, mvb200::pf::g_trace, sizeof(mvb200::pf::g_trace));
+}
+extern "C" __attribute__((visibility("default"))) int mvb200_debug_read_prefill_ctas(unsigned long long* dst) {
+  return (int)cudaMemcpyFromSymbol(dst, mvb200::pf::g_cta, sizeof(mvb200::pf::g_cta));
+}
+#endif

@@ -45,6 +45,30 @@ MVB_DEV uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t
   return d;
 }
 
+// The same descriptor as two 32-bit halves: the high half depends only on SBO, the low half advances
+// linearly with the start address — (lo + (bytes >> 4)) steps through a tile — so an issue loop keeps
+// both in uniform registers and never rebuilds the descriptor.
+__host__ __device__ constexpr uint32_t umma_desc_hi(uint32_t sbo_bytes) {
+  return ((sbo_bytes >> 4) & 0x3FFF) | (1u << 14) | (2u << 29);
+}
+MVB_DEV uint32_t umma_desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr >> 4) & 0x3FFF) | (((lbo_bytes >> 4) & 0x3FFF) << 16);
+}
+MVB_DEV uint64_t umma_desc(uint32_t hi, uint32_t lo) { return ((uint64_t)hi << 32) | lo; }
+
+// One lane of a converged warp (the others skip): the role loops stay warp-uniform, so their operands
+// live in uniform registers and tcgen05.mma / TMA issue is a single predicated instruction instead of
+// a per-lane waterfall loop (which costs ~80 cycles per MMA when the loop runs under `if (lane == 0)`).
+MVB_DEV bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // Instruction descriptor for kind::f16 (cute::UMMA::InstrDescriptor), fp32 accumulate:
 //   [4,6) D format = 1 (f32) | [7,10) A format | [10,13) B format (0 = f16, 1 = bf16)
 //   [15] A major, [16] B major (0 = K-major, 1 = MN-major) | [17,23) N >> 3 | [24,29) M >> 4
