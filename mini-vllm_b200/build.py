@@ -15,6 +15,7 @@ SOURCES = [
     "paged_decode.cu",
     "prefill_generic.cu",
     "prefill_tcgen05.cu",
+    "prefill_fa2q.cu",
     "prefill_api.cu",
 ]
 NVCC_FLAGS = [

@@ -16,8 +16,9 @@ int prefill_generic_dispatch(const void* q, int64_t q_row_stride, const void* k,
                              int64_t num_blocks, int max_blocks, float scale, int dtype,
                              cudaStream_t stream);
 
-// returns -1 when the request is outside what the tcgen05 kernel covers
-int prefill_tcgen05_dispatch(const PrefillArgs& a, cudaStream_t stream);
+// return -1 when the request is outside what the kernel covers
+int prefill_tcgen05_dispatch(const PrefillArgs& a, cudaStream_t stream);  // one query tile per CTA
+int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream);     // persistent, two query tiles per CTA
 
 }  // namespace mvb200
 
@@ -53,8 +54,11 @@ extern "C" int mvb200_prefill_varlen(
                 num_seqs, total_q, max_seqlen_q, max_seqlen_k, num_heads, num_kv_heads, head_dim,
                 block_size, num_blocks, max_blocks_per_seq, scale, dtype};
   const bool force_generic = getenv("MVB200_PREFILL_GENERIC") != nullptr;  // debugging aid
+  const bool force_v1 = getenv("MVB200_PREFILL_V1") != nullptr;            // A/B profiling aid
   if (!force_generic) {
-    const int rc = prefill_tcgen05_dispatch(a, s);
+    int rc = force_v1 ? -1 : prefill_fa2q_dispatch(a, s);
+    if (rc >= 0) return rc;
+    rc = prefill_tcgen05_dispatch(a, s);
     if (rc >= 0) return rc;
   }
   return prefill_generic_dispatch(q, q_row_stride, k, v, k_row_stride, v_row_stride, k_cache,

@@ -459,7 +459,7 @@ def test_prefill_tcgen05_ragged_paged(m, cuda_device, bs, dtype):
         torch.from_numpy(pr["cu_q"]).to(cuda_device), torch.from_numpy(pr["cu"]).to(cuda_device),
         max(pr["lq"]), max(lens), scale, k_cache=pr["kc"], v_cache=pr["vc"], block_tables=pr["bt"],
     )
-    assert m.ops.last_kernel() == "prefill_tcgen05"
+    assert m.ops.last_kernel().startswith("prefill_tcgen05")
     full = orc.prefill_dense(_f32(pr["q"]), _f32(pr["k"]), _f32(pr["v"]), pr["cu"], pr["cu"], scale)
     got = _f32(out)
     assert np.isfinite(got).all()
@@ -480,7 +480,7 @@ def test_prefill_tcgen05_dense_strided_source(m, cuda_device):
     cu = np.concatenate([[0], np.cumsum(lens)]).astype(np.int32)
     cut = torch.from_numpy(cu).to(cuda_device)
     out = m.prefill_varlen_attention(q, k, v, cut, cut, max(lens), max(lens), d**-0.5)
-    assert m.ops.last_kernel() == "prefill_tcgen05"
+    assert m.ops.last_kernel().startswith("prefill_tcgen05")
     ref = orc.prefill_dense(_f32(q), _f32(k), _f32(v), cu, cu, d**-0.5)
     assert np.abs(_f32(out) - ref).max() <= TOL["bf16"]
 
@@ -505,7 +505,7 @@ def test_prefill_full_size_against_oracle_samples(m, cuda_device, name, lens, ca
         torch.from_numpy(pr["cu_q"]).to(cuda_device), torch.from_numpy(pr["cu"]).to(cuda_device),
         max(pr["lq"]), max(lens), scale, k_cache=pr["kc"], v_cache=pr["vc"], block_tables=pr["bt"],
     )
-    assert m.ops.last_kernel() == "prefill_tcgen05"
+    assert m.ops.last_kernel().startswith("prefill_tcgen05")
     got = _f32(out)
     assert np.isfinite(got).all()
     heads = sorted({0, h // 2, h - 1})
@@ -535,4 +535,4 @@ def test_prefill_kernel_selection(m, cuda_device):
         q = torch.randn(10, 2, d, device=cuda_device).to(dt)
         cu = torch.tensor([0, 10], dtype=torch.int32, device=cuda_device)
         m.prefill_varlen_attention(q, q, q, cu, cu, 10, 10, 0.1)
-        assert m.ops.last_kernel() == want
+        assert m.ops.last_kernel().startswith(want)
