@@ -59,6 +59,18 @@ MVB_DEV bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// Non-blocking probe (no suspend): for a role that polls several barriers.
+MVB_DEV bool mbar_test(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
 // Spin on try_wait (which itself sleeps in hardware).  A barrier that never flips is a protocol bug:
 // trap after ~2 s of SM clocks instead of hanging the device.
 MVB_DEV void mbar_wait(uint32_t bar, uint32_t parity) {

@@ -36,33 +36,52 @@ using pf::fma2;
 using pf::pack2;
 using pf::unpack2;
 
+// Pipeline trace (debug builds only, -DPF_TRACE; tools/prefill_trace.py): CTA 0 records clock64 at the
+// hand-offs of its MMA issuer (role 0) and of one warp of each softmax warpgroup (roles 1, 2) for the
+// first item it runs.
+#ifdef PF_TRACE
+__device__ unsigned long long g_trace2[4 * 64 * 8];
+#define PF2_T(role, j, ev)                                                                    \
+  do {                                                                                        \
+    if (traced && (j) < 64) {                                                                 \
+      unsigned long long t_;                                                                  \
+      asm volatile("mov.u64 %0, %%clock64;" : "=l"(t_)::"memory");                            \
+      g_trace2[((role) * 64 + (j)) * 8 + (ev)] = t_;                                          \
+    }                                                                                         \
+  } while (0)
+#else
+#define PF2_T(role, j, ev) do {} while (0)
+#endif
+
 constexpr int kD = 128;
 constexpr int kBM = 128;                 // rows per query tile
 constexpr int kQTiles = 2;               // query tiles per work item
 constexpr int kBN = 128;                 // keys per K/V tile
 constexpr int kPage = 64;                // keys per TMA box (= kvcache_block_size granularity)
 constexpr int kStages = 2;               // K ring depth = V ring depth
-constexpr int kThreads = 320;
+constexpr int kThreads = 384;
+constexpr int kMaxPChunks = 4;            // P is handed to the MMA warp in kPC (1, 2 or 4) column chunks per tile
 constexpr int kTileHalfBytes = 128 * 128;  // [128 rows][128 B] = one 64-column half of a tile
 constexpr int kTileBytes = 2 * kTileHalfBytes;
 constexpr int kBoxBytes = kPage * 128;     // one TMA box: 64 rows x 64 columns
 constexpr int kTmemCols = 512;
 constexpr int kColS = 0, kColO = 256;      // + t * 128
 constexpr int kMaxLevels = 512;            // query blocks per sequence (256 rows each): 131072 tokens
+constexpr int kDefaultPChunks = 1;
 constexpr int kDefaultEmu = 32;            // of every 128 columns, exponentials done on the FMA pipe
 constexpr float kRescaleThreshold = 8.f;   // log2 domain: rescale O only when the max grew by > 2^8
 
 enum {
-  BAR_Q_FULL = 0,    // [2]  TMA -> MMA
-  BAR_Q_EMPTY = 2,   // [2]  MMA (commit after the item's last Q K^T) -> TMA
+  BAR_Q_FULL = 0,    // [2]  TMA -> MMA warp t
+  BAR_Q_EMPTY = 2,   // [2]  MMA warp t (commit after the item's last Q_t K^T) -> TMA
   BAR_K_FULL = 4,    // [kStages]
-  BAR_K_EMPTY = 6,
+  BAR_K_EMPTY = 6,   // [kStages]  MMA (commit after the last Q_t K^T that reads the stage) -> TMA
   BAR_V_FULL = 8,
   BAR_V_EMPTY = 10,
-  BAR_S_FULL = 12,   // [2]  MMA -> softmax warpgroup t
-  BAR_P_FULL = 14,   // [2]  softmax warpgroup t (4 warp arrivals) -> MMA
-  BAR_O_DONE = 16,   // [2]  MMA (commit after every P V of tile t) -> softmax warpgroup t
-  BAR_COUNT = 18
+  BAR_S_FULL = 12,   // [2]  MMA warp t -> softmax warpgroup t
+  BAR_O_DONE = 14,   // [2]  MMA warp t (commit after every P_t V) -> softmax warpgroup t
+  BAR_P_FULL = 16,   // [2][kMaxPChunks]  softmax warpgroup t (4 warp arrivals) -> MMA warp t, per column chunk of P
+  BAR_COUNT = 16 + 2 * kMaxPChunks
 };
 
 struct Params {
@@ -122,7 +141,7 @@ MVB_DEV Item decode_item(const Params& p, int w) {
   return it;
 }
 
-template <typename T, int kEmu>
+template <typename T, int kEmu, int kPC>
 __global__ void __launch_bounds__(kThreads, 1)
 prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
                     const __grid_constant__ CUtensorMap tmap_k,
@@ -146,7 +165,9 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
     tmem_relinquish();
   }
   if (threadIdx.x == 32) {
-    for (int i = 0; i < BAR_COUNT; ++i) mbar_init(bar(i), (i == BAR_P_FULL || i == BAR_P_FULL + 1) ? 4 : 1);
+    for (int i = 0; i < BAR_COUNT; ++i) {
+      mbar_init(bar(i), i >= BAR_P_FULL ? 4 : 1);
+    }
     fence_mbar_init();
   }
   tc_fence_before();
@@ -236,6 +257,11 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
     }
   } else if (warp == 1) {
     // =========================== MMA issuer ===========================
+    // Each query tile is a serial chain  S_t(j) -> softmax -> P_t(j) V(j) -> S_t(j+1)  (S_t(j+1) overwrites
+    // P_t(j) in TMEM); the two chains interleave on the one tensor pipe, block by block.  P arrives in kPC
+    // column chunks, so P V starts while the warpgroup still exponentiates.  Measured alternatives, both
+    // slower: one issuing warp per tile (their MMAs interleave one by one and both chains stretch) and
+    // a polling event loop over both chains (a poll pass costs ~500 cycles next to the softmax warps).
     constexpr uint32_t idesc_qk = umma_idesc(kBM, kBN, kBf16, false, false);
     constexpr uint32_t idesc_pv = umma_idesc(kBM, kD, kBf16, false, true);
     constexpr uint32_t desc_hi = umma_desc_hi(1024);  // 8-row (K-major) / 8-key (MN-major) groups 1 KiB apart
@@ -243,7 +269,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const uint32_t k_lo0 = umma_desc_lo(sK, 16);
     const uint32_t v_lo0 = umma_desc_lo(sV, kTileHalfBytes);  // LBO = distance between the 64-column halves
     uint32_t q_uses[kQTiles] = {0, 0};
-    uint32_t p_cnt[kQTiles] = {0, 0};
+    uint32_t p_cnt[kQTiles] = {0, 0};   // P tiles consumed so far (phase of the P_FULL barriers)
     uint32_t kv_cnt = 0;
 
     // S_t = Q_t K_s^T : 8 k-steps of 16 elements (32 B inside the 128-B swizzle row, halves 16 KiB apart)
@@ -257,31 +283,23 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
         umma_ss(s_col, umma_desc(desc_hi, q_lo + off), umma_desc(desc_hi, k_lo + off), idesc_qk, kk > 0 ? 1u : 0u);
       }
     };
-    // O_t (+)= P_t V_s : A = bf16 P in TMEM (8 columns per 16 keys), B = V MN-major, 16 keys = 2 KiB
-    auto issue_pv = [&](int t, int s, int ksteps, bool first) {
-      const uint32_t v_lo = v_lo0 + s * (kTileBytes >> 4);
-      const uint32_t p_col = tmem + kColS + t * kBN;
-      const uint32_t o_col = tmem + kColO + t * kD;
-#pragma unroll
-      for (int kk = 0; kk < kBN / 16; ++kk) {
-        if (kk < ksteps)
-          umma_ts(o_col, p_col + kk * 8, umma_desc(desc_hi, v_lo + kk * (16 * 128 >> 4)), idesc_pv,
-                  (!first || kk > 0) ? 1u : 0u);
-      }
-    };
 
     for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
       const Item it = decode_item(p, w);
       if (!it.valid || it.n_kt == 0) continue;
-#pragma unroll
-      for (int t = 0; t < kQTiles; ++t) {
-        if (it.n[t] == 0) continue;
-        mbar_wait(bar(BAR_Q_FULL + t), q_uses[t] & 1);
-        ++q_uses[t];
-      }
+#ifdef PF_TRACE
+      const bool traced = blockIdx.x == 0 && w == (int)blockIdx.x + (int)gridDim.x && lane == 0;
+#endif
+      PF2_T(0, 62, 0);
       // ---- prologue: S_t(0) ----
       {
         const int s = kv_cnt % kStages;
+#pragma unroll
+        for (int t = 0; t < kQTiles; ++t) {
+          if (it.n[t] == 0) continue;
+          mbar_wait(bar(BAR_Q_FULL + t), q_uses[t] & 1);
+          ++q_uses[t];
+        }
         mbar_wait(bar(BAR_K_FULL + s), (kv_cnt / kStages) & 1);
         tc_fence_after();
         if (elect_one()) {
@@ -296,7 +314,9 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
         }
         __syncwarp();
       }
-      // ---- main loop: per K/V tile j and query tile t:  O_t += P_t(j) V(j);  S_t(j+1) = Q_t K(j+1)^T ----
+      // ---- main loop: per K/V tile j and query tile t:  O_t += P_t(j) V(j) chunk by chunk, then
+      //      S_t(j+1) = Q_t K(j+1)^T.  Blocking waits in chain order: the two chains run half a period apart,
+      //      so while this warp follows tile t's chunks the other warpgroup is still exponentiating. ----
       for (int j = 0; j < it.n_kt; ++j) {
         const uint32_t cnt = kv_cnt + j;
         const int s = cnt % kStages, s_next = (cnt + 1) % kStages;
@@ -306,36 +326,59 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
         for (int t = 0; t < kQTiles; ++t) {
           if (j >= it.n[t]) continue;
           const bool more = j + 1 < it.n[t];
-          if (more && !k_next_ready) {
-            mbar_wait(bar(BAR_K_FULL + s_next), ((cnt + 1) / kStages) & 1);
-            k_next_ready = true;
-          }
-          mbar_wait(bar(BAR_P_FULL + t), p_cnt[t] & 1);
-          ++p_cnt[t];
-          tc_fence_after();
           // last consumer of V(j) / K(j+1) among the query tiles: the highest t that still uses it
           const bool last_v = (t == kQTiles - 1) || (j >= it.n[t + 1 < kQTiles ? t + 1 : t]);
           const bool last_k = (t == kQTiles - 1) || (j + 1 >= it.n[t + 1 < kQTiles ? t + 1 : t]);
           const int ksteps = more ? kBN / 16 : (it.kv_end[t] - j * kBN + 15) / 16;
-          if (elect_one()) {
-            issue_pv(t, s, ksteps, j == 0);
-            umma_commit(bar(BAR_O_DONE + t));
-            if (last_v) umma_commit(bar(BAR_V_EMPTY + s));
-            if (more) {
+          const uint32_t v_lo = v_lo0 + s * (kTileBytes >> 4);
+          const uint32_t p_col = tmem + kColS + t * kBN;
+          const uint32_t o_col = tmem + kColO + t * kD;
+#pragma unroll
+          for (int ch = 0; ch < kPC; ++ch) {
+            mbar_wait(bar(BAR_P_FULL + t * kMaxPChunks + ch), p_cnt[t] & 1);
+            if (ch == 0) PF2_T(t, j, 1);
+            tc_fence_after();
+            if (elect_one()) {
+              // A = bf16 P in TMEM (8 columns per 16 keys), B = V MN-major, 16 keys = 2 KiB
+#pragma unroll
+              for (int kk = ch * (8 / kPC); kk < (ch + 1) * (8 / kPC); ++kk) {
+                if (kk < ksteps)
+                  umma_ts(o_col, p_col + kk * 8, umma_desc(desc_hi, v_lo + kk * (16 * 128 >> 4)), idesc_pv,
+                          (j > 0 || kk > 0) ? 1u : 0u);
+              }
+              if (ch == kPC - 1) {
+                umma_commit(bar(BAR_O_DONE + t));
+                if (last_v) umma_commit(bar(BAR_V_EMPTY + s));
+              }
+            }
+            __syncwarp();
+          }
+          ++p_cnt[t];
+          PF2_T(t, j, 4);
+          if (more) {
+            if (!k_next_ready) {
+              mbar_wait(bar(BAR_K_FULL + s_next), ((cnt + 1) / kStages) & 1);
+              k_next_ready = true;
+              tc_fence_after();
+            }
+            if (elect_one()) {
               issue_qk(t, s_next);
               umma_commit(bar(BAR_S_FULL + t));
               if (j + 2 == it.n[t]) umma_commit(bar(BAR_Q_EMPTY + t));
               if (last_k) umma_commit(bar(BAR_K_EMPTY + s_next));
             }
+            __syncwarp();
           }
-          __syncwarp();
+          PF2_T(t, j, 6);
         }
       }
       kv_cnt += it.n_kt;
     }
+  } else if (warp < 4) {
+    // idle warps: keep the softmax warpgroups aligned to TMEM lane quarters (warp % 4)
   } else {
     // =========================== softmax warpgroups (thread = query row) ===========================
-    const int t = (warp - 2) >> 2;                // query tile of this warpgroup
+    const int t = (warp - 4) >> 2;                // query tile of this warpgroup
     const int quarter = warp & 3;                 // TMEM lanes this warp may touch
     const int r = quarter * 32 + lane;            // query row within the tile
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
@@ -363,11 +406,16 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
           for (int i = 0; i < kD; i += 8) *reinterpret_cast<uint4*>(orow + i) = make_uint4(0, 0, 0, 0);
         continue;
       }
+#ifdef PF_TRACE
+      const bool traced = blockIdx.x == 0 && w == (int)blockIdx.x + (int)gridDim.x && lane == 0 && quarter == 0;
+#endif
       const int q_limit = it.shift + row0_t + r;  // largest key index this row may see
       float m_ref = -INFINITY, l_run = 0.f;
 
       for (int j = 0; j < n_t; ++j, ++c) {
+        PF2_T(2 + t, j, 0);
         mbar_wait(bar(BAR_S_FULL + t), c & 1);
+        PF2_T(2 + t, j, 1);
         tc_fence_after();
         float s[kBN];
         {
@@ -375,6 +423,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
 #pragma unroll
           for (int g = 0; g < 4; ++g) tmem_ld32(s_col + 32 * g, raw[g]);
           tmem_wait_ld();
+          PF2_T(2 + t, j, 2);
 #pragma unroll
           for (int g = 0; g < 4; ++g)
 #pragma unroll
@@ -386,10 +435,14 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
 #pragma unroll
           for (int i = 0; i < kBN; ++i) s[i] = i <= lim ? s[i] : -INFINITY;
         }
-        float mx = fmaxf(s[0], s[1]);
+        float mx4[4];  // four independent chains of 3-input max (a single chain is 64 dependent ops)
 #pragma unroll
-        for (int i = 2; i < kBN; i += 2) mx = fmaxf(mx, fmaxf(s[i], s[i + 1]));
-        mx *= p.scale_log2;
+        for (int q4 = 0; q4 < 4; ++q4) {
+          mx4[q4] = fmaxf(s[32 * q4], s[32 * q4 + 1]);
+#pragma unroll
+          for (int i = 2; i < 32; i += 2) mx4[q4] = fmaxf(mx4[q4], fmaxf(s[32 * q4 + i], s[32 * q4 + i + 1]));
+        }
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
         // lazy rescale: keep exponentiating against m_ref until the true max outruns it by 2^8
         const bool grow = mx > m_ref + kRescaleThreshold;
         if (__any_sync(0xffffffffu, grow)) {
@@ -411,37 +464,6 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
           }
           m_ref = m_new;
         }
-        const float m_use = m_ref == -INFINITY ? 0.f : m_ref;
-        const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
-        const uint64_t negm2 = pack2(-m_use, -m_use);
-        uint64_t sum2 = pack2(0.f, 0.f);
-#pragma unroll
-        for (int chunk = 0; chunk < 4; ++chunk) {
-          uint32_t pk[16];
-#pragma unroll
-          for (int i = 0; i < 32; i += 2) {
-            const int col = chunk * 32 + i;
-            const uint64_t x = fma2(pack2(s[col], s[col + 1]), scale2, negm2);
-            float p0, p1;
-            // kEmu of every 128 columns take the FMA-pipe exponential, interleaved with the MUFU ones
-            if (kEmu > 0 && ((col / 2) * (kEmu / 2)) % (kBN / 2) < kEmu / 2) {
-              ex2_poly2(x, p0, p1);
-            } else {
-              float x0, x1;
-              unpack2(x, x0, x1);
-              p0 = ex2_mufu(x0);
-              p1 = ex2_mufu(x1);
-            }
-            sum2 = add2(sum2, pack2(p0, p1));
-            pk[i / 2] = Mma16816<T>::pack(p0, p1);
-          }
-          tmem_st16(s_col + chunk * 16, pk);  // bf16 P overwrites the first 64 columns of S_t
-        }
-        float sum_lo, sum_hi;
-        unpack2(sum2, sum_lo, sum_hi);
-        l_run += sum_lo + sum_hi;
-        tmem_wait_st();
-
         if (j == n_t - 1 && quarter == 0) {
           // keys >= Lk in the last block were never written: their V rows may hold NaN/Inf bit patterns and
           // 0 * NaN would poison O.  Zero those inside the last 16-key group the MMA reads (whole groups
@@ -460,9 +482,45 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
             fence_proxy_async_smem();
           }
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar(BAR_P_FULL + t));
+        const float m_use = m_ref == -INFINITY ? 0.f : m_ref;
+        PF2_T(2 + t, j, 3);
+        const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
+        const uint64_t negm2 = pack2(-m_use, -m_use);
+        uint64_t sum2[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};  // two chains: FADD2 latency off the critical path
+#pragma unroll
+        for (int chunk = 0; chunk < 4; ++chunk) {
+          uint32_t pk[16];
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) {
+            const int col = chunk * 32 + i;
+            const uint64_t x = fma2(pack2(s[col], s[col + 1]), scale2, negm2);
+            float p0, p1;
+            // kEmu of every 128 columns take the FMA-pipe exponential, interleaved with the MUFU ones
+            if (kEmu > 0 && ((col / 2) * (kEmu / 2)) % (kBN / 2) < kEmu / 2) {
+              ex2_poly2(x, p0, p1);
+            } else {
+              float x0, x1;
+              unpack2(x, x0, x1);
+              p0 = ex2_mufu(x0);
+              p1 = ex2_mufu(x1);
+            }
+            sum2[(i >> 1) & 1] = add2(sum2[(i >> 1) & 1], pack2(p0, p1));
+            pk[i / 2] = Mma16816<T>::pack(p0, p1);
+          }
+          tmem_st16(s_col + chunk * 16, pk);  // bf16 P overwrites the first 64 columns of S_t
+          if ((chunk + 1) % (4 / kPC) == 0) {  // hand this part of P to the MMA warp
+            tmem_wait_st();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(BAR_P_FULL + t * kMaxPChunks + chunk / (4 / kPC)));
+          }
+        }
+        float sum_lo, sum_hi;
+        unpack2(add2(sum2[0], sum2[1]), sum_lo, sum_hi);
+        l_run += sum_lo + sum_hi;
+        PF2_T(2 + t, j, 4);
+
+        PF2_T(2 + t, j, 6);
       }
 
       // ---- epilogue: O / l -> global ----
@@ -486,6 +544,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
           }
         }
       }
+      PF2_T(2 + t, 63, 0);
       tc_fence_before();  // the next item's first P V (accumulate = 0) overwrites O after our next P_FULL arrival
     }
   }
@@ -495,7 +554,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   if (warp == 0) tmem_dealloc(tmem, kTmemCols);
 }
 
-template <typename T, int kEmu>
+template <typename T, int kEmu, int kPC>
 static int launch(const PrefillArgs& a, cudaStream_t stream) {
   CUtensorMap mq, mk, mv;
   {
@@ -544,7 +603,7 @@ static int launch(const PrefillArgs& a, cudaStream_t stream) {
   p.scale_log2 = a.scale * kLog2e;
 
   constexpr int smem = (kQTiles + 2 * kStages) * kTileBytes + 8 * BAR_COUNT + 16 + 1024;
-  auto kern = prefill_fa2q_kernel<T, kEmu>;
+  auto kern = prefill_fa2q_kernel<T, kEmu, kPC>;
   static thread_local bool configured = false;
   static thread_local int num_sms = 0;
   if (!configured) {
@@ -583,20 +642,32 @@ int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream) {
   }
   note_kernel("prefill_tcgen05_2q");
   // Columns (of every 128) whose exponential runs on the FMA pipe instead of MUFU.  Tuning knob for
-  // profiling only (MVB200_PREFILL_EMU = 0 | 16 | 32 | 48 | 64); the default is the measured optimum.
+  // profiling only (MVB200_PREFILL_EMU = 0 | 16 | 32 | 48, MVB200_PREFILL_PCHUNKS = 1 | 2 | 4); the default is the measured optimum.
   static const int emu = [] {
     const char* e = getenv("MVB200_PREFILL_EMU");
     const int v = e ? atoi(e) : fa2q::kDefaultEmu;
-    return (v == 0 || v == 16 || v == 32 || v == 48 || v == 64) ? v : fa2q::kDefaultEmu;
+    return (v == 0 || v == 16 || v == 32 || v == 48) ? v : fa2q::kDefaultEmu;
+  }();
+  static const int pchunks = [] {
+    const char* e = getenv("MVB200_PREFILL_PCHUNKS");
+    const int v = e ? atoi(e) : fa2q::kDefaultPChunks;
+    return (v == 1 || v == 2 || v == 4) ? v : fa2q::kDefaultPChunks;
   }();
   const bool bf = a.dtype == MVB200_BF16;
-  switch (emu) {
-    case 0: return bf ? fa2q::launch<__nv_bfloat16, 0>(a, stream) : fa2q::launch<__half, 0>(a, stream);
-    case 16: return bf ? fa2q::launch<__nv_bfloat16, 16>(a, stream) : fa2q::launch<__half, 16>(a, stream);
-    case 48: return bf ? fa2q::launch<__nv_bfloat16, 48>(a, stream) : fa2q::launch<__half, 48>(a, stream);
-    case 64: return bf ? fa2q::launch<__nv_bfloat16, 64>(a, stream) : fa2q::launch<__half, 64>(a, stream);
-    default: return bf ? fa2q::launch<__nv_bfloat16, 32>(a, stream) : fa2q::launch<__half, 32>(a, stream);
-  }
+#define MVB_FA2Q_CASE(E, C) \
+  if (emu == E && pchunks == C) return bf ? fa2q::launch<__nv_bfloat16, E, C>(a, stream) : fa2q::launch<__half, E, C>(a, stream);
+  MVB_FA2Q_CASE(0, 1) MVB_FA2Q_CASE(0, 2) MVB_FA2Q_CASE(0, 4)
+  MVB_FA2Q_CASE(16, 1) MVB_FA2Q_CASE(16, 2) MVB_FA2Q_CASE(16, 4)
+  MVB_FA2Q_CASE(32, 1) MVB_FA2Q_CASE(32, 2) MVB_FA2Q_CASE(32, 4)
+  MVB_FA2Q_CASE(48, 1) MVB_FA2Q_CASE(48, 2) MVB_FA2Q_CASE(48, 4)
+#undef MVB_FA2Q_CASE
+  return fail(MVB200_EINVAL, "prefill: no kernel instance for emu %d / pchunks %d", emu, pchunks);
 }
 
 }  // namespace mvb200
+
+#ifdef PF_TRACE
+extern "C" __attribute__((visibility("default"))) int mvb200_debug_read_prefill2_trace(unsigned long long* dst) {
+  return (int)cudaMemcpyFromSymbol(dst, mvb200::fa2q::g_trace2, sizeof(mvb200::fa2q::g_trace2));
+}
+#endif

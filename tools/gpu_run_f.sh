@@ -1,0 +1,13 @@
+#!/bin/bash
+set -u
+mkdir -p gpurun_out
+timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "prefill or layer or smoke" > gpurun_out/pytest_prefill.txt 2>&1; echo "pytest exit $?"; tail -5 gpurun_out/pytest_prefill.txt
+for emu in ${EMUS:-0 16 32 48}; do
+  MVB200_PREFILL_EMU=$emu timeout 300 python bench.py --workload cfg3p --steps 10 --no-cpu-baseline > gpurun_out/cfg3p_emu$emu.json 2> gpurun_out/cfg3p_emu$emu.err; echo "emu $emu exit $?"
+  python -c "import json;d=json.load(open('gpurun_out/cfg3p_emu$emu.json'));print('emu',$emu,d['roofline']['kernel'],d['roofline']['achieved'],d['roofline']['us_per_launch'],d['clocks'])"
+done
+for emu in ${EMUS1:-32}; do
+MVB200_PREFILL_EMU=$emu timeout 300 python bench.py --workload cfg3p1 --steps 10 --no-cpu-baseline > gpurun_out/cfg3p1_emu$emu.json 2>&1
+python -c "import json;d=json.load(open('gpurun_out/cfg3p1_emu$emu.json'));print('cfg3p1 emu$emu',d['roofline']['achieved'],d['roofline']['us_per_launch'],d['clocks'])"
+done
+MVB200_PREFILL_EMU=${TRACE_EMU:-32} timeout 120 python tools/prefill_trace.py > gpurun_out/prefill2_trace.log 2>&1; echo "trace exit $?"

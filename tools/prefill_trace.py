@@ -14,6 +14,9 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 os.environ["MVB200_LIB"] = os.path.join(ROOT, "mini-vllm_b200", "libmvb200_trace.so")
+V1 = "--v1" in sys.argv  # trace the one-query-tile kernel instead of the persistent two-tile one
+if V1:
+    os.environ["MVB200_PREFILL_V1"] = "1"
 
 import numpy as np
 import torch
@@ -38,6 +41,8 @@ def main():
     for _ in range(3):
         out = m.ops.prefill_varlen_attention(q, None, None, cu_q, cu_k, NQ, lk, D**-0.5, k_cache=kc, v_cache=vc, block_tables=perm)
     torch.cuda.synchronize()
+    if not V1:
+        return report_v2()
     buf = (ctypes.c_ulonglong * (3 * 64 * 8))()
     fn = _native.lib().mvb200_debug_read_prefill_trace
     fn.argtypes = [ctypes.c_void_p]
@@ -65,6 +70,41 @@ def main():
     for j in range(n):
         r = t[0, j]
         print(f"  {j:2d} | @{rel(r[0]):7d} | Kempty +{r[1]-r[0]:5d} | Vempty +{r[2]-r[1]:5d}")
+
+
+def report_v2():
+    """Second work item of CTA 0 (steady state: its loads were prefetched during the first)."""
+    buf = (ctypes.c_ulonglong * (4 * 64 * 8))()
+    fn = _native.lib().mvb200_debug_read_prefill2_trace
+    fn.argtypes = [ctypes.c_void_p]
+    assert fn(buf) == 0
+    t = np.frombuffer(buf, dtype=np.uint64).astype(np.int64).reshape(4, 64, 8)
+    t0 = t[0, 62, 0]
+    rel = lambda x: int(x - t0)
+    n = 17
+    for q in (0, 1):
+        print(f"MMA issuer, chain of query tile {q}: j | first P chunk issued @ | last chunk issued | QK(j+1) issued | period")
+        prev = None
+        for j in range(n):
+            r = t[q, j]
+            if r[1] == 0 or r[1] < t0:
+                break
+            per = (r[1] - prev) if prev is not None else 0
+            prev = r[1]
+            qk = f"qk +{r[6]-r[4]:5d}" if r[6] > r[4] else "qk   (none)"
+            print(f"  {j:2d} | @{rel(r[1]):7d} | lastP +{r[4]-r[1]:5d} | {qk} | period {per:5d}")
+    for wg in (0, 1):
+        print(f"softmax warpgroup {wg}: j | wait S_full | LDTM | mask/max/rescale | exp+STTM+arrivals | busy | period")
+        prev = None
+        for j in range(n):
+            r = t[2 + wg, j]
+            if r[1] == 0 or r[1] < t[0, 62, 0]:
+                break
+            per = (r[6] - prev) if prev is not None else 0
+            prev = r[6]
+            print(f"  {j:2d} | @{rel(r[0]):7d} | S_full +{r[1]-r[0]:5d} | ld +{r[2]-r[1]:4d} | max +{r[3]-r[2]:4d} | exp +{r[4]-r[3]:4d} "
+                  f"| busy {r[6]-r[1]:5d} | period {per:5d}")
+        print(f"  epilogue done @{rel(t[2 + wg, 63, 0])}")
 
 
 def cta_report(num_ctas):
