@@ -25,10 +25,34 @@ int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, int rank
                     const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
                     bool swizzle128);
 
+// Launch with programmatic stream serialization (PDL): the kernel may start while its predecessor in
+// the stream drains; it must execute pdl_wait() before it touches anything a predecessor wrote (or
+// still reads).  Capturable into CUDA graphs.  MVB200_NO_PDL=1 falls back to a plain launch.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                              cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 // ---------------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------------
 #define MVB_DEV __device__ __forceinline__
+
+// ---- programmatic dependent launch ----
+MVB_DEV void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+MVB_DEV void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 MVB_DEV uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

@@ -1,6 +1,7 @@
 // host_util.cu — error plumbing and TMA descriptor encoding for libmvb200.
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -24,6 +25,14 @@ int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(MVB200_ECUDA, "%s: %s", what, cudaGetErrorString(e));
   return MVB200_OK;
+}
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("MVB200_NO_PDL");
+    return !(e && e[0] && e[0] != '0');
+  }();
+  return on;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,

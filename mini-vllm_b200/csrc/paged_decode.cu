@@ -77,6 +77,22 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
   const int lane = threadIdx.x & 31;
   const int G = p.group;
 
+  // prologue that needs nothing from earlier kernels runs before the dependency wait (PDL)
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < stages; ++s) {
+      mbar_init(bar_base + 8 * s, 1);                           // full: producer's expect_tx arrive
+      mbar_init(bar_base + 8 * (stages + s), kConsumerWarps);   // empty: one arrive per warp
+    }
+    fence_mbar_init();
+  }
+  if (threadIdx.x == kConsumerWarps * 32) {
+    tma_prefetch_desc(&tmap_k);
+    tma_prefetch_desc(&tmap_v);
+  }
+  __syncthreads();
+  pdl_wait();               // q, context_lens, block tables and the freshly stored K/V are visible from here
+  pdl_launch_dependents();  // the split reduction (or the next layer's kernel) may start its own prologue
+
   const int ctx = p.context_lens[b];
   const int n_tiles = ctx > 0 ? (ctx + kTileTokens - 1) / kTileTokens : 0;
   const int tps = (n_tiles + p.num_splits - 1) / p.num_splits;
@@ -98,15 +114,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
     return;
   }
 
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < stages; ++s) {
-      mbar_init(bar_base + 8 * s, 1);                           // full: producer's expect_tx arrive
-      mbar_init(bar_base + 8 * (stages + s), kConsumerWarps);   // empty: one arrive per warp
-    }
-    fence_mbar_init();
-  }
-  __syncthreads();
-
   // per-warp running state (consumer warps only)
   float o_acc[D / 8][4];
   float m_run[2] = {-INFINITY, -INFINITY};
@@ -114,10 +121,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
 
   if (warp == kConsumerWarps) {
     // ------------------------------ producer warp ------------------------------
-    if (lane == 0) {
-      tma_prefetch_desc(&tmap_k);
-      tma_prefetch_desc(&tmap_v);
-    }
     const int n = t1 - t0;
     const int32_t* bt = p.block_tables + (int64_t)b * p.bt_row_stride;
     for (int base = 0; base < n; base += 32) {
@@ -333,28 +336,54 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
 }
 
 // Combine the per-split partials: out = sum_s w_s o_s / sum_s w_s, w_s = 2^(lse_s - max lse).
+// One CTA per (head, sequence); the four warps take interleaved splits so that the partial rows of
+// different splits are in flight together (a serial walk over 128 splits costs more than the decode
+// kernel itself at batch 1), lanes cover head_dim with coalesced 128-byte rows.
 template <typename T>
 __global__ void __launch_bounds__(128)
 decode_reduce_kernel(const float* __restrict__ part_o, const float* __restrict__ part_lse,
                      T* __restrict__ out, int64_t out_row_stride, int num_heads, int head_dim,
                      int num_splits) {
+  constexpr int kMaxPerLane = 8;  // head_dim <= 256
+  __shared__ float sm_acc[4][256];
+  __shared__ float sm_w[4], sm_max[4];
   const int h = blockIdx.x, b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t ph = ((int64_t)b * num_heads + h) * num_splits;
-  float M = -INFINITY;
-  for (int s = 0; s < num_splits; ++s) M = fmaxf(M, part_lse[ph + s]);
-  for (int d = threadIdx.x; d < head_dim; d += blockDim.x) {
-    float acc = 0.f, wsum = 0.f;
-    if (M != -INFINITY) {
-      for (int s = 0; s < num_splits; ++s) {
-        const float lse = part_lse[ph + s];
-        if (lse == -INFINITY) continue;
-        const float w = exp2f(lse - M);
-        wsum += w;
-        acc += w * part_o[(ph + s) * head_dim + d];
+  pdl_wait();  // partials come from the decode kernel launched just before
+  pdl_launch_dependents();
+  float m = -INFINITY;
+  for (int s = threadIdx.x; s < num_splits; s += 128) m = fmaxf(m, part_lse[ph + s]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if (lane == 0) sm_max[warp] = m;
+  __syncthreads();
+  const float M = fmaxf(fmaxf(sm_max[0], sm_max[1]), fmaxf(sm_max[2], sm_max[3]));
+  float acc[kMaxPerLane];
+#pragma unroll
+  for (int i = 0; i < kMaxPerLane; ++i) acc[i] = 0.f;
+  float wsum = 0.f;
+  if (M != -INFINITY) {
+    for (int s = warp; s < num_splits; s += 4) {
+      const float lse = part_lse[ph + s];
+      const float w = lse == -INFINITY ? 0.f : exp2f(lse - M);  // empty split: its row is never read as data
+      wsum += w;
+      const float* row = part_o + (ph + s) * head_dim;
+#pragma unroll
+      for (int i = 0; i < kMaxPerLane; ++i) {
+        const int d = lane + 32 * i;
+        if (d < head_dim && w != 0.f) acc[i] += w * row[d];
       }
     }
-    out[(int64_t)b * out_row_stride + (int64_t)h * head_dim + d] =
-        from_f32<T>(wsum > 0.f ? acc / wsum : 0.f);
+  }
+#pragma unroll
+  for (int i = 0; i < kMaxPerLane; ++i) sm_acc[warp][lane + 32 * i] = acc[i];
+  if (lane == 0) sm_w[warp] = wsum;
+  __syncthreads();
+  const float W = sm_w[0] + sm_w[1] + sm_w[2] + sm_w[3];
+  for (int d = threadIdx.x; d < head_dim; d += 128) {
+    const float o = sm_acc[0][d] + sm_acc[1][d] + sm_acc[2][d] + sm_acc[3][d];
+    out[(int64_t)b * out_row_stride + (int64_t)h * head_dim + d] = from_f32<T>(W > 0.f ? o / W : 0.f);
   }
 }
 
@@ -466,14 +495,18 @@ static int launch_fast(const DecodeParams& p, const void* k_cache, const void* v
     configured = smem;
   }
   dim3 grid(p.num_kv_heads, p.num_splits, batch);
-  kern<<<grid, kDecodeThreads, smem, stream>>>(mk, mv, p);
+  cudaError_t le = launch_pdl(kern, grid, dim3(kDecodeThreads), (size_t)smem, stream, mk, mv, p);
+  if (le != cudaSuccess)
+    return fail(MVB200_ECUDA, "paged_decode_kernel: %s", cudaGetErrorString(le));
   rc = check_launch("paged_decode_kernel");
   if (rc) return rc;
   if (p.num_splits > 1) {
     dim3 rgrid(p.num_heads, batch);
-    decode_reduce_kernel<T><<<rgrid, 128, 0, stream>>>(p.part_o, p.part_lse, (T*)p.out,
-                                                       p.out_row_stride, p.num_heads, D,
-                                                       p.num_splits);
+    le = launch_pdl(decode_reduce_kernel<T>, rgrid, dim3(128), 0, stream, (const float*)p.part_o,
+                    (const float*)p.part_lse, (T*)p.out, p.out_row_stride, p.num_heads, D,
+                    p.num_splits);
+    if (le != cudaSuccess)
+      return fail(MVB200_ECUDA, "decode_reduce_kernel: %s", cudaGetErrorString(le));
     rc = check_launch("decode_reduce_kernel");
   }
   return rc;
@@ -518,8 +551,12 @@ extern "C" int32_t mvb200_decode_suggest_splits(int32_t batch, int32_t num_kv_he
   if (sm_count <= 0) sm_count = 148;
   const int64_t units = (int64_t)batch * num_kv_heads;
   const int tiles = max_context > 0 ? (max_context + 63) / 64 : 1;
-  const int64_t want = 4LL * sm_count;  // CTAs: two resident per SM, two waves
-  int64_t s = (want + units - 1) / units;
+  // Plenty of (sequence, kv head) units: two waves of two resident CTAs per SM.  Fewer units than SMs
+  // (long-context, small-batch decode): one CTA per SM in a single wave — measured on B200 at
+  // 1 x 32k x 4 kv heads: 128 CTAs 21 us, 296 CTAs 27 us, 512 CTAs 36 us (per-CTA prologue and the
+  // split reduction grow with the split count).
+  const int64_t want = units >= sm_count ? 4LL * sm_count : (int64_t)sm_count;
+  int64_t s = units >= sm_count ? (want + units - 1) / units : want / units;
   const int max_by_work = tiles / 4 > 0 ? tiles / 4 : 1;  // keep >= 4 tiles (128 KiB) per CTA
   if (s > max_by_work) s = max_by_work;
   if (s < 1) s = 1;

@@ -17,6 +17,8 @@ store_kvcache_kernel(const char* __restrict__ key, const char* __restrict__ valu
                      char* __restrict__ k_cache, char* __restrict__ v_cache,
                      const int32_t* __restrict__ slot_mapping, int64_t total_vecs,
                      int32_t vecs_per_row, int64_t num_slots) {
+  pdl_wait();  // key/value/slot_mapping come from the kernels before; the cache may still be read by them
+  pdl_launch_dependents();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t row_bytes = (int64_t)vecs_per_row * sizeof(Vec);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total_vecs; i += stride) {
@@ -41,9 +43,10 @@ static int launch_store(const void* key, const void* value, int64_t ks_bytes, in
   int64_t blocks = (total + threads - 1) / threads;
   const int64_t cap = 148LL * 32;  // grid-stride beyond 32 CTAs per SM
   if (blocks > cap) blocks = cap;
-  store_kvcache_kernel<Vec><<<(unsigned)blocks, threads, 0, stream>>>(
-      (const char*)key, (const char*)value, ks_bytes, vs_bytes, (char*)k_cache, (char*)v_cache,
-      slots, total, vpr, num_slots);
+  cudaError_t e = launch_pdl(store_kvcache_kernel<Vec>, dim3((unsigned)blocks), dim3(threads), 0, stream,
+                             (const char*)key, (const char*)value, ks_bytes, vs_bytes,
+                             (char*)k_cache, (char*)v_cache, slots, total, vpr, num_slots);
+  if (e != cudaSuccess) return fail(MVB200_ECUDA, "store_kvcache: %s", cudaGetErrorString(e));
   return check_launch("store_kvcache");
 }
 

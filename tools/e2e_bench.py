@@ -33,6 +33,7 @@ def main():
     ap.add_argument("--max-model-len", type=int, default=4096)
     ap.add_argument("--eager", action="store_true")
     ap.add_argument("--repeat", type=int, default=2)
+    ap.add_argument("--profile", default="", help="write a torch.profiler per-kernel table of one more pass to this file")
     args = ap.parse_args()
 
     import torch
@@ -70,6 +71,17 @@ def main():
         st["hit_tokens"] = (eng.pool.hits - hits0) * 64
         if best is None or st["decode_s"] < best["decode_s"]:
             best = st
+    if args.profile:
+        import contextlib
+
+        from torch.profiler import ProfilerActivity, profile
+        prompts = [torch.randint(lo, hi, (args.prompt,), generator=g).tolist() for _ in range(args.seqs)]
+        with (profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) if rank == 0 else contextlib.nullcontext()) as prof:
+            eng.generate(prompts, min(args.new_tokens, 16))
+    if args.profile and rank == 0:
+        with open(args.profile, "w") as f:
+            f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=40, max_name_column_width=90))
+            f.write("\n" + json.dumps(eng.stats) + "\n")
     if rank == 0:
         new_prefill = best["prefill_tokens"]
         print(json.dumps({
