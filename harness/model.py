@@ -9,6 +9,7 @@ row-parallel ``o_proj``/``down_proj`` (layers/linear.py:316-319).
 
 from __future__ import annotations
 
+import os
 import zlib
 from dataclasses import dataclass
 
@@ -16,6 +17,8 @@ import torch
 import torch.distributed as dist
 import torch.nn.functional as F
 from torch import nn
+
+from . import fused
 
 
 @dataclass
@@ -106,30 +109,43 @@ class DecoderLayer(nn.Module):
             self.q_norm = self.k_norm = None
         self.rotary = rotary  # shared cos/sin tables
         self.attn = attention_cls(self.h, self.d, self.d ** -0.5, self.kvh)
+        self.fused_rope = os.environ.get("MVB200_HARNESS_UNFUSED", "0") in ("", "0")
+
+    def _norm(self, x, weight, residual):
+        if self.fused_rope and x.is_cuda:  # harness/csrc/fused_elementwise.cu
+            return fused.add_rms_norm(x, weight, self.cfg.rms_eps, residual)
+        if residual is None:
+            return rms_norm(x, weight, self.cfg.rms_eps)[0], x
+        return rms_norm(x, weight, self.cfg.rms_eps, residual)
 
     def forward(self, positions, x, residual):
         cfg = self.cfg
-        if residual is None:
-            residual = x
-            x, _ = rms_norm(x, self.in_norm, cfg.rms_eps)
-        else:
-            x, residual = rms_norm(x, self.in_norm, cfg.rms_eps, residual)
+        x, residual = self._norm(x, self.in_norm, residual)
         n = x.size(0)
         qkv = F.linear(x, self.qkv_w, self.qkv_b)
         q, k, v = qkv.split([self.h * self.d, self.kvh * self.d, self.kvh * self.d], dim=-1)
         q, k, v = q.view(n, self.h, self.d), k.view(n, self.kvh, self.d), v.view(n, self.kvh, self.d)
-        if self.q_norm is not None:
-            q, _ = rms_norm(q, self.q_norm, cfg.rms_eps)
-            k, _ = rms_norm(k, self.k_norm, cfg.rms_eps)
-        q, k = self.rotary(positions, q, k)
-        o = self.attn(q, k, v).reshape(n, self.h * self.d)
+        if self.fused_rope and q.is_cuda and hasattr(self.attn, "forward_fused"):
+            # one kernel for q/k norm + RoPE + cache store
+            o = self.attn.forward_fused(positions, q, k, v, self.rotary.cos, self.rotary.sin,
+                                        self.q_norm, self.k_norm, cfg.rms_eps).reshape(n, self.h * self.d)
+        else:
+            if self.q_norm is not None:
+                q, _ = rms_norm(q, self.q_norm, cfg.rms_eps)
+                k, _ = rms_norm(k, self.k_norm, cfg.rms_eps)
+            q, k = self.rotary(positions, q, k)
+            o = self.attn(q, k, v).reshape(n, self.h * self.d)
         o = F.linear(o, self.o_w)
         if self.tp > 1:
             dist.all_reduce(o)
-        x, residual = rms_norm(o, self.post_norm, cfg.rms_eps, residual)
+        x, residual = self._norm(o, self.post_norm, residual)
         gu = F.linear(x, self.gate_up_w)
-        g, u = gu.chunk(2, dim=-1)
-        x = F.linear(F.silu(g) * u, self.down_w)
+        if self.fused_rope and gu.is_cuda:
+            act = fused.silu_mul(gu)
+        else:
+            g, u = gu.chunk(2, dim=-1)
+            act = F.silu(g) * u
+        x = F.linear(act, self.down_w)
         if self.tp > 1:
             dist.all_reduce(x)
         return x, residual
@@ -150,6 +166,8 @@ class QwenLM(nn.Module):
         residual = None
         for layer in self.layers:
             x, residual = layer(positions, x, residual)
+        if x.is_cuda and self.layers[0].fused_rope:
+            return fused.add_rms_norm(x, self.final_norm, self.cfg.rms_eps, residual)[0]
         x, _ = rms_norm(x, self.final_norm, self.cfg.rms_eps, residual)
         return x
 

@@ -128,6 +128,35 @@ MVB200_API int mvb200_prefill_varlen(const void* q, int64_t q_row_stride,
                           int32_t block_size, int64_t num_blocks, int32_t max_blocks_per_seq,
                           float scale, int32_t dtype, void* stream);
 
+/*
+ * qk_norm_rope_store — caller-side fusion in front of the attention layer.
+ * Replaces the sequence in QwenAttention.forward, models/qwen_base.py:181-186:
+ *   q_norm / k_norm  (RMSNorm over head_dim, models/layers/layernorm.py:81-93; Qwen3 only)
+ *   rotary_emb       (models/layers/rotary_embedding.py:166-193, apply_rotary_emb :78-84)
+ * and the store Attention.forward begins with (models/layers/attention.py:228-243,
+ * models/layers/attention_backend.py:196-266).
+ *
+ * For every token i and head h:   x = q[i,h,:] (or k[i,h,:])
+ *   if weights given: x = T( float(x) * (1/sqrt(mean(float(x)^2) + eps)) * float(w) )
+ *   c, s = cos_cache[pos], sin_cache[pos]   pos = clamp(positions[i], 0, max_positions-1), tables fp32 [max_positions, D/2]
+ *   out[0:D/2] = T( x1*c - x2*s ),  out[D/2:D] = T( x2*c + x1*s )      x1, x2 = halves of float(x)
+ * q_out / k_out receive the result (they may alias q / k: in place; k_out may be NULL), and for
+ * 0 <= slot_mapping[i] < num_slots the rotated k row and the untouched v row are written to
+ * k_cache / v_cache row slot_mapping[i] ([num_slots, KVH*D]).  slot_mapping NULL: no store.
+ * q_norm_weight / k_norm_weight: [D] in the model dtype, both NULL for models without q/k norm.
+ */
+MVB200_API int mvb200_qk_norm_rope_store(const void* q, int64_t q_row_stride,
+                          const void* k, int64_t k_row_stride,
+                          const void* v, int64_t v_row_stride,
+                          void* q_out, int64_t q_out_row_stride,
+                          void* k_out, int64_t k_out_row_stride,
+                          const int64_t* positions,
+                          const float* cos_cache, const float* sin_cache, int64_t max_positions,
+                          const void* q_norm_weight, const void* k_norm_weight, float eps,
+                          const int32_t* slot_mapping, void* k_cache, void* v_cache, int64_t num_slots,
+                          int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads,
+                          int32_t head_dim, int32_t dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -44,6 +44,15 @@ SIGNATURES = {
          c_int32, c_int32, c_int32, c_int32, c_int32, c_int32, c_int32,
          c_int32, c_int64, c_int32, c_float, c_int32, c_void_p],
     ),
+    "mvb200_qk_norm_rope_store": (
+        c_int32,
+        [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64,
+         c_void_p, c_int64, c_void_p, c_int64,
+         c_void_p, c_void_p, c_void_p, c_int64,
+         c_void_p, c_void_p, c_float,
+         c_void_p, c_void_p, c_void_p, c_int64,
+         c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p],
+    ),
 }
 
 

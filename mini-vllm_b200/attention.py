@@ -79,7 +79,31 @@ class Attention(nn.Module):
             f"num_kv_heads={self.num_kv_heads}, scale={self.scale}, backend=mvb200(sm_100a)"
         )
 
-    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+    def forward_fused(
+        self,
+        positions: torch.Tensor,
+        q: torch.Tensor,
+        k: torch.Tensor,
+        v: torch.Tensor,
+        cos_cache: torch.Tensor,
+        sin_cache: torch.Tensor,
+        q_norm_weight: torch.Tensor | None = None,
+        k_norm_weight: torch.Tensor | None = None,
+        eps: float = 1e-6,
+    ) -> torch.Tensor:
+        """``q_norm/k_norm -> rotary_emb -> self.attn(q, k, v)`` of qwen_base.py:181-186 with the
+        norm, the rotation and the cache store done by ONE kernel.  ``q, k, v`` are
+        the raw views of the fused qkv GEMM output; q and k are rotated in place."""
+        context = _get_context()
+        k_cache, v_cache = self.k_cache, self.v_cache
+        has_cache = k_cache.numel() > 0 and v_cache.numel() > 0
+        fusable = not has_cache or q.dtype == k_cache.dtype
+        slots = context.slot_mapping if has_cache and fusable else None
+        q, k = ops.qk_norm_rope_store(q, k, v, positions, cos_cache, sin_cache, q_norm_weight, k_norm_weight,
+                                      eps, slots, k_cache if has_cache else None, v_cache if has_cache else None)
+        return self.forward(q, k, v, _stored=fusable)
+
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, _stored: bool = False) -> torch.Tensor:
         context = _get_context()
         k_cache, v_cache = self.k_cache, self.v_cache
         has_cache = k_cache.numel() > 0 and v_cache.numel() > 0
@@ -90,7 +114,7 @@ class Attention(nn.Module):
         if has_cache:
             self._cache_initialized = True
             slots = context.slot_mapping
-            if slots is not None and slots.numel() > 0:  # attention.py:237-243
+            if not _stored and slots is not None and slots.numel() > 0:  # attention.py:237-243
                 ops.store_kvcache(k, v, k_cache, v_cache, slots)
         elif not context.is_prefill and not self._cache_initialized:
             raise RuntimeError(

@@ -12,6 +12,7 @@ LIB = os.path.join(HERE, "libmvb200.so")
 SOURCES = [
     "host_util.cu",
     "store_kvcache.cu",
+    "qk_rope_store.cu",
     "paged_decode.cu",
     "prefill_generic.cu",
     "prefill_tcgen05.cu",

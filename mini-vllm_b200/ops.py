@@ -9,6 +9,7 @@ Reference call sites (relative to the reference repository):
   store_kvcache              attention_backend.py:196-266 (+ Triton kernel :52-78)
   paged_decode_attention     attention.py:439-447, page_attention.py:35-133
   prefill_varlen_attention   attention.py:396-433, :467-504
+  qk_norm_rope_store         qwen_base.py:181-186 + attention.py:228-243 (caller-side fusion)
 """
 
 from __future__ import annotations
@@ -114,6 +115,90 @@ def store_kvcache(
         n, row, k_cache.numel() // row, _code(k_cache.dtype), _stream(),
     )
     _native.check(rc, "mvb200_store_kvcache")
+
+
+# ---------------------------------------------------------------------------
+# q/k RMSNorm + RoPE + store (caller-side fusion)
+# ---------------------------------------------------------------------------
+
+
+def qk_norm_rope_store(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    positions: torch.Tensor,
+    cos_cache: torch.Tensor,
+    sin_cache: torch.Tensor,
+    q_norm_weight: torch.Tensor | None = None,
+    k_norm_weight: torch.Tensor | None = None,
+    eps: float = 1e-6,
+    slot_mapping: torch.Tensor | None = None,
+    k_cache: torch.Tensor | None = None,
+    v_cache: torch.Tensor | None = None,
+    *,
+    inplace: bool = True,
+) -> tuple[torch.Tensor, torch.Tensor]:
+    """One kernel for ``q_norm``/``k_norm`` -> ``rotary_emb`` -> ``store_kv_cache``.
+
+    Replaces qwen_base.py:181-186 plus the store of attention.py:228-243: RMSNorm over
+    ``head_dim`` (layernorm.py:81-93, skipped when the weights are ``None`` — Qwen2), rotation with
+    ``cos_cache/sin_cache[positions]`` (fp32 ``[max_pos, D/2]``, rotary_embedding.py:150-193), and
+    the scatter of the rotated ``k`` and of ``v`` to ``slot_mapping`` (``None`` or empty: no store).
+    Returns ``(q, k)`` rotated — the inputs themselves when ``inplace`` (they are views of the
+    fused qkv GEMM output that nothing else reads), fresh tensors otherwise.
+    """
+    _require_cuda(q, k, v, positions, cos_cache, sin_cache, q_norm_weight, k_norm_weight, slot_mapping, k_cache, v_cache)
+    n, h, d = q.shape
+    kvh = k.size(1)
+    if k.shape != (n, kvh, d) or v.shape != (n, kvh, d):
+        raise ValueError(f"q {tuple(q.shape)}, k {tuple(k.shape)}, v {tuple(v.shape)} are inconsistent")
+    if positions.numel() != n:
+        raise ValueError(f"positions size {positions.numel()} != num_tokens {n}")
+    if k.dtype != q.dtype or v.dtype != q.dtype:
+        raise ValueError("q, k, v must share a dtype")
+    if cos_cache.dtype != torch.float32 or sin_cache.dtype != torch.float32:
+        raise ValueError("cos/sin caches must be float32 (rotary_embedding.py:157-165)")
+    if cos_cache.dim() != 2 or cos_cache.size(1) * 2 != d or sin_cache.shape != cos_cache.shape:
+        raise ValueError(f"cos/sin caches must be [max_pos, {d // 2}], got {tuple(cos_cache.shape)}")
+    if (q_norm_weight is None) != (k_norm_weight is None):
+        raise ValueError("q_norm_weight and k_norm_weight must be given together")
+    for w in (q_norm_weight, k_norm_weight):
+        if w is not None and (w.numel() != d or w.dtype != q.dtype):
+            raise ValueError("norm weights must be [head_dim] in the activation dtype")
+    store = slot_mapping is not None and slot_mapping.numel() > 0 and k_cache is not None and k_cache.numel() > 0
+    num_slots = 0
+    if store:
+        if slot_mapping.numel() != n:
+            raise ValueError(f"slot_mapping size {slot_mapping.numel()} != batch_size {n}")
+        if k_cache.dtype != q.dtype or v_cache.dtype != q.dtype:
+            raise ValueError("cache dtype must equal the activation dtype for the fused store")
+        if not (k_cache.is_contiguous() and v_cache.is_contiguous()):
+            raise ValueError("k_cache / v_cache must be contiguous")
+        num_slots = k_cache.numel() // (kvh * d)
+    if n == 0:
+        return q, k
+    q, k, v = _rows(q), _rows(k), _rows(v)
+    q_out, k_out = (q, k) if inplace else (torch.empty_like(q, memory_format=torch.contiguous_format),
+                                           torch.empty_like(k, memory_format=torch.contiguous_format))
+    pos = positions.reshape(-1)
+    if pos.dtype != torch.int64 or not pos.is_contiguous():
+        pos = pos.to(torch.int64).contiguous()
+    slots = None
+    if store:
+        slots = _i32(slot_mapping.reshape(-1), q.device).contiguous()
+    cos_cache, sin_cache = cos_cache.contiguous(), sin_cache.contiguous()
+    rc = _native.lib().mvb200_qk_norm_rope_store(
+        q.data_ptr(), _row_stride(q), k.data_ptr(), _row_stride(k), v.data_ptr(), _row_stride(v),
+        q_out.data_ptr(), _row_stride(q_out), k_out.data_ptr(), _row_stride(k_out),
+        pos.data_ptr(), cos_cache.data_ptr(), sin_cache.data_ptr(), cos_cache.size(0),
+        q_norm_weight.data_ptr() if q_norm_weight is not None else None,
+        k_norm_weight.data_ptr() if k_norm_weight is not None else None, float(eps),
+        slots.data_ptr() if store else None,
+        k_cache.data_ptr() if store else None, v_cache.data_ptr() if store else None, num_slots,
+        n, h, kvh, d, _code(q.dtype), _stream(),
+    )
+    _native.check(rc, "mvb200_qk_norm_rope_store")
+    return q_out, k_out
 
 
 # ---------------------------------------------------------------------------

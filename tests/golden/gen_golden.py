@@ -20,6 +20,8 @@ stored as uint16 bit patterns.  What is recorded:
 * ``prefill_*`` : ``Attention._fallback_attention`` prefill branch (attention.py:467-504)
 * ``layer_*``   : ``Attention.forward`` prefill then decode steps through the
                   real ``Context`` (attention.py:196-455), caches included
+* ``qkrope``    : ``RMSNorm`` on q/k + ``RotaryEmbedding`` + store, the caller-side sequence of
+                  ``QwenAttention.forward`` (qwen_base.py:175-186)
 """
 
 from __future__ import annotations
@@ -525,11 +527,71 @@ def gen_engine():
     save("engine", **out)
 
 
+# ---------------------------------------------------------------------------
+# caller side: q/k RMSNorm -> RoPE -> store, as QwenAttention.forward does it
+# ---------------------------------------------------------------------------
+
+
+def gen_qkrope():
+    """``QwenAttention.forward`` between the qkv GEMM and ``self.attn`` (qwen_base.py:175-186):
+    ``RMSNorm`` on q and k (layernorm.py:81-93), ``RotaryEmbedding.forward`` (rotary_embedding.py:166-193),
+    then the store of the new K/V rows that ``Attention.forward`` performs first (attention.py:228-236)."""
+    from minivllm.models.layers.layernorm import RMSNorm
+    from minivllm.models.layers.rotary_embedding import RotaryEmbedding
+
+    backend = StandardAttentionBackend()
+    out = {}
+    cases = [
+        # name, N, H, KVH, D, dtype, qk-norm, max_pos, rope base, num_slots
+        ("qwen3_bf16", 37, 4, 2, 128, torch.bfloat16, True, 256, 1000000.0, 128),
+        ("qwen2_bf16_nonorm", 20, 7, 1, 128, torch.bfloat16, False, 256, 1000000.0, 64),
+        ("f16_norm", 11, 4, 2, 128, torch.float16, True, 128, 10000.0, 64),
+        ("f32_d64", 9, 3, 3, 64, torch.float32, True, 64, 10000.0, 32),
+    ]
+    for idx, (name, n, h, kvh, d, dt, norm, max_pos, base, slots_n) in enumerate(cases):
+        g = torch.Generator().manual_seed(700 + idx)
+        fused = randn(g, n, (h + 2 * kvh) * d, dtype=dt) * 2.0
+        q, k, v = fused.split([h * d, kvh * d, kvh * d], dim=-1)
+        q, k, v = q.view(n, h, d), k.view(n, kvh, d), v.view(n, kvh, d)
+        positions = torch.randint(0, max_pos, (n,), generator=g, dtype=torch.int64)
+        slots = torch.randperm(slots_n, generator=g)[:n].to(torch.int32)
+        slots[1] = -1
+        rope = RotaryEmbedding(d, d, max_pos, base)
+        qn, kn = q, k
+        if norm:
+            q_norm, k_norm = RMSNorm(d, eps=1e-6), RMSNorm(d, eps=1e-6)
+            q_norm.weight.data = (1.0 + 0.1 * randn(g, d)).to(dt)
+            k_norm.weight.data = (1.0 + 0.1 * randn(g, d)).to(dt)
+            qn, _ = q_norm(q)
+            kn, _ = k_norm(k)
+            out[f"{name}.q_weight"] = to_np(q_norm.weight.data)
+            out[f"{name}.k_weight"] = to_np(k_norm.weight.data)
+        qr, kr = rope(positions, qn, kn)
+        k_cache = randn(g, slots_n, kvh * d, dtype=dt)
+        v_cache = randn(g, slots_n, kvh * d, dtype=dt)
+        out[f"{name}.k_cache_in"] = to_np(k_cache)
+        out[f"{name}.v_cache_in"] = to_np(v_cache)
+        backend.store_kv_cache(kr, v, k_cache, v_cache, slots)
+        out[f"{name}.fused"] = to_np(fused)
+        out[f"{name}.positions"] = to_np(positions)
+        out[f"{name}.slots"] = to_np(slots)
+        out[f"{name}.cos"] = to_np(rope.cos_cache)
+        out[f"{name}.sin"] = to_np(rope.sin_cache)
+        out[f"{name}.q_out"] = to_np(qr)
+        out[f"{name}.k_out"] = to_np(kr)
+        out[f"{name}.k_cache_out"] = to_np(k_cache)
+        out[f"{name}.v_cache_out"] = to_np(v_cache)
+        out[f"{name}.meta"] = np.array([n, h, kvh, d, int(norm), max_pos, slots_n])
+        out[f"{name}.base"] = np.array(base)
+        out[f"{name}.eps"] = np.array(1e-6)
+        out[f"{name}.dtype"] = np.array(dtype_name(dt))
+    out["cases"] = np.array([c[0] for c in cases])
+    save("qkrope", **out)
+
+
 if __name__ == "__main__":
     print("generating golden vectors from", REFERENCE)
-    gen_store()
-    gen_decode()
-    gen_prefill()
-    gen_layer()
-    gen_metadata()
-    gen_engine()
+    only = set(sys.argv[1:])
+    for fn in (gen_store, gen_decode, gen_prefill, gen_layer, gen_metadata, gen_engine, gen_qkrope):
+        if not only or fn.__name__[4:] in only:
+            fn()

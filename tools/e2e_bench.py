@@ -33,9 +33,14 @@ def main():
     ap.add_argument("--max-model-len", type=int, default=4096)
     ap.add_argument("--eager", action="store_true")
     ap.add_argument("--repeat", type=int, default=2)
+    ap.add_argument("--watchdog", type=int, default=0, help="dump every thread's Python stack and exit after this many seconds")
     ap.add_argument("--profile", default="", help="write a torch.profiler per-kernel table of one more pass to this file")
     args = ap.parse_args()
 
+    if args.watchdog:
+        import faulthandler
+
+        faulthandler.dump_traceback_later(args.watchdog, exit=True)
     import torch
     import torch.distributed as dist
 
@@ -94,8 +99,13 @@ def main():
             "prefix_hit_tokens": best["hit_tokens"], "engine_init_s": t_init,
         }), flush=True)
     if world > 1:
+        # The captured decode graphs hold NCCL kernels; destroy_process_group() with them alive blocks forever
+        # (seen on 2 x B200, torch 2.11 / NCCL 2.28).  Drain, then leave without tearing the communicator down.
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 if __name__ == "__main__":
