@@ -11,6 +11,7 @@ simplest thing that exercises the path: all prompts are prefilled (in batches bo
 from __future__ import annotations
 
 import hashlib
+import os
 import struct
 import time
 from collections import deque
@@ -113,6 +114,7 @@ class BlockPool:
             bid = self._take()
             self.hash_of[bid], self.tokens_of[bid] = -1, None
             seq.block_table.append(bid)
+            return bid
         elif n % bs == 0:
             last = seq.block_table[-1]
             prefix = self.hash_of[seq.block_table[-2]] if len(seq.block_table) > 1 else -1
@@ -120,6 +122,7 @@ class BlockPool:
             h = self.compute_hash(toks, prefix)
             self.hash_of[last], self.tokens_of[last] = h, toks
             self.by_hash[h] = last
+        return None
 
     def deallocate(self, seq: Seq):
         for bid in reversed(seq.block_table):
@@ -133,7 +136,7 @@ class BlockPool:
 class Engine:
     def __init__(self, cfg: ModelConfig, *, device, dtype=torch.bfloat16, tp=1, rank=0, max_num_seqs=256,
                  max_model_len=4096, max_num_batched_tokens=16384, num_blocks=None, enforce_eager=False,
-                 init="fast", attention_cls=None, seed=1234):
+                 init="fast", attention_cls=None, seed=1234, device_loop=None):
         self.cfg, self.device, self.dtype, self.tp, self.rank = cfg, torch.device(device), dtype, tp, rank
         self.max_num_seqs, self.max_model_len = max_num_seqs, max_model_len
         self.max_num_batched_tokens = max_num_batched_tokens
@@ -157,8 +160,14 @@ class Engine:
         self.exe.allocate_kv_cache(num_blocks)
         self.pool = BlockPool(num_blocks)
         self.enforce_eager = enforce_eager
-        if not enforce_eager and self.device.type == "cuda":
-            self.exe.capture_graphs()
+        # device-resident decode bookkeeping (decode_advance + greedy_argmax inside the graph); the host
+        # loop of the reference (prepare_decode every step) stays available for A/B: MVB200_HARNESS_HOST_LOOP=1
+        if device_loop is None:
+            device_loop = os.environ.get("MVB200_HARNESS_HOST_LOOP", "0") in ("", "0")
+        self.device_loop = bool(device_loop) and self.device.type == "cuda"
+        if self.device.type == "cuda" and (self.device_loop or not enforce_eager):
+            self.exe.capture_graphs(token_fn=self.model.pick_tokens if self.device_loop else None,
+                                    capture=not enforce_eager)
         self.stats: dict[str, float] = {}
 
     def _sync(self):
@@ -178,13 +187,15 @@ class Engine:
     def generate(self, prompts, max_tokens, forced=None, return_logits=False):
         """Greedy generation.  ``forced[i][t]``, when given, is appended instead of the argmax (teacher
         forcing for parity tests); the model's own choice and logits are still returned."""
-        seqs = [Seq(p, max_tokens) for p in prompts]
+        per_seq = isinstance(max_tokens, (list, tuple))
+        seqs = [Seq(p, max_tokens[i] if per_seq else max_tokens) for i, p in enumerate(prompts)]
         picked = [[] for _ in seqs]
         logits_log = [[] for _ in seqs]
         order = {id(s): i for i, s in enumerate(seqs)}
 
-        def emit(batch, hidden, step_of):
-            toks = self.model.greedy_tokens(hidden).tolist()
+        def emit(batch, hidden, step_of, toks=None):
+            if toks is None:
+                toks = self.model.greedy_tokens(hidden).tolist()
             lg = self.model.compute_logits(hidden).float().cpu() if return_logits else None
             for j, s in enumerate(batch):
                 i = order[id(s)]
@@ -217,14 +228,27 @@ class Engine:
         self._sync()
         t1 = time.perf_counter()
         steps = 0
+        loop_rows = None
+        use_loop = self.device_loop and forced is None
         while True:
             live = [s for s in running if not s.done]
             if not live:
                 break
-            for s in live:
-                self.pool.may_append(s)
-            hidden = self.exe.run(live, False, use_graph=not self.enforce_eager)
-            emit(live, hidden, steps)
+            appends = {}
+            for j, s in enumerate(live):
+                bid = self.pool.may_append(s)
+                if bid is not None:
+                    appends[j] = bid
+            if use_loop:
+                rows = [id(s) for s in live]
+                if rows != loop_rows:  # (re)load the persistent device state; it already holds the new blocks
+                    self.exe.begin_decode(live)
+                    loop_rows, appends = rows, None
+                toks = self.exe.step_decode(appends).tolist()
+                emit(live, self.exe.graph_vars["outputs"][:len(live)], steps, toks)
+            else:
+                hidden = self.exe.run(live, False, use_graph=not self.enforce_eager)
+                emit(live, hidden, steps)
             steps += 1
         self._sync()
         t2 = time.perf_counter()

@@ -191,6 +191,28 @@ class QwenLM(nn.Module):
         win = allp[..., 0].argmax(dim=0)
         return allp[win, torch.arange(hidden.size(0), device=hidden.device), 1].long()
 
+    def pick_tokens(self, hidden, out):
+        """Greedy pick on the device into ``out`` (int64 [B]) with the mvb200 argmax kernel; capturable.
+        Vocabulary-sharded across TP ranks: every rank reduces its slice, a tiny all-gather of (value,
+        index) pairs picks the winner (lowest rank, hence lowest index, on ties)."""
+        from minivllm_b200 import ops
+
+        w = self.embed if self.lm_head is None else self.lm_head
+        if self.tp == 1:
+            ops.greedy_argmax(F.linear(hidden, w), out)
+            return
+        per = (self.cfg.vocab_size + self.tp - 1) // self.tp
+        lo, hi = self.rank * per, min(self.cfg.vocab_size, (self.rank + 1) * per)
+        b = hidden.size(0)
+        val = torch.empty(b, dtype=torch.float32, device=hidden.device)
+        idx = torch.empty(b, dtype=torch.int64, device=hidden.device)
+        ops.greedy_argmax(F.linear(hidden, w[lo:hi]), idx, out_value=val, index_offset=lo)
+        pack = torch.stack([val, idx.float()], dim=-1)
+        allp = torch.empty(self.tp, b, 2, dtype=torch.float32, device=hidden.device)
+        dist.all_gather_into_tensor(allp.view(self.tp * b, 2), pack)
+        win = allp[..., 0].argmax(dim=0)
+        out.copy_(allp[win, torch.arange(b, device=hidden.device), 1].long())
+
     # ---- weights -------------------------------------------------------------------------------
     def reference_names(self):
         """(harness parameter, reference parameter name, TP slicing rule) for every tensor."""

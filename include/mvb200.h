@@ -157,6 +157,35 @@ MVB200_API int mvb200_qk_norm_rope_store(const void* q, int64_t q_row_stride,
                           int32_t num_tokens, int32_t num_heads, int32_t num_kv_heads,
                           int32_t head_dim, int32_t dtype, void* stream);
 
+/*
+ * decode_advance — advance the persistent decode metadata by one token, on the device.
+ * Replaces, per step, InferenceExecutor._prepare_decode_input (engine/inference_executor.py:551-617),
+ * _prepare_block_tables_decode (:651-688) and the graph-buffer refill of _execute_with_cuda_graph
+ * (:751-768).  For every row b < batch with context_lens[b] > 0 (len = context_lens[b] + 1):
+ *   if appends[b] >= 0: block_tables[b, (len-1)/block_size] = appends[b]     (the block handed out by
+ *                                                     BlockManager.may_append when len % BS == 1)
+ *   input_ids[b] = next_tokens[b];  positions[b] = len-1;  context_lens[b] = len
+ *   slot_mapping[b] = block_tables[b, (len-1)/block_size]*block_size + (len-1)%block_size   (:568-572)
+ *                     (-1 when that entry is negative, >= num_blocks or beyond max_blocks)
+ * Rows with context_lens[b] <= 0 are graph-bucket padding: input_ids = positions = 0, slot = -1 (:757-760).
+ * appends[b] is reset to -1 for every row.  All tensors are the persistent (graph) buffers; no host sync.
+ */
+MVB200_API int mvb200_decode_advance(const int64_t* next_tokens, int32_t* appends, int64_t* input_ids,
+                          int64_t* positions, int32_t* slot_mapping, int32_t* context_lens,
+                          int32_t* block_tables, int64_t bt_row_stride, int32_t batch,
+                          int32_t max_blocks, int32_t block_size, int64_t num_blocks, void* stream);
+
+/*
+ * greedy_argmax — the temperature == 0 branch of the reference sampler (sampling/sampler.py:104-106;
+ * GreedySampler :118-130): out_index[r] = index_offset + argmax_j logits[r, j], ties to the lowest j,
+ * NaN counts as the maximum (torch.argmax).  out_value (optional, fp32) receives the maximum itself so
+ * vocabulary-sharded ranks can combine their winners.  workspace: mvb200_greedy_argmax_workspace_bytes.
+ */
+MVB200_API size_t mvb200_greedy_argmax_workspace_bytes(int32_t rows, int32_t vocab);
+MVB200_API int mvb200_greedy_argmax(const void* logits, int64_t row_stride, int32_t rows, int32_t vocab,
+                          int32_t dtype, void* workspace, size_t workspace_bytes,
+                          int64_t* out_index, float* out_value, int64_t index_offset, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -53,6 +53,17 @@ SIGNATURES = {
          c_void_p, c_void_p, c_void_p, c_int64,
          c_int32, c_int32, c_int32, c_int32, c_int32, c_void_p],
     ),
+    "mvb200_decode_advance": (
+        c_int32,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+         c_int32, c_int32, c_int32, c_int64, c_void_p],
+    ),
+    "mvb200_greedy_argmax_workspace_bytes": (c_size_t, [c_int32, c_int32]),
+    "mvb200_greedy_argmax": (
+        c_int32,
+        [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_size_t,
+         c_void_p, c_void_p, c_int64, c_void_p],
+    ),
 }
 
 

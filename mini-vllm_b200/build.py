@@ -13,6 +13,7 @@ SOURCES = [
     "host_util.cu",
     "store_kvcache.cu",
     "qk_rope_store.cu",
+    "decode_meta.cu",
     "paged_decode.cu",
     "prefill_generic.cu",
     "prefill_tcgen05.cu",

@@ -12,7 +12,11 @@ block/slot layout; what changes:
 * graph outputs are allocated in the model dtype and the whole ``[bs, hidden]``
   hidden state is copied (the reference copies row 0 of it);
 * a fixed KV split count and its workspace are part of the captured state;
-* host-side prep is vectorised (numpy) instead of per-token Python loops.
+* host-side prep is vectorised (numpy) instead of per-token Python loops;
+* optionally (``capture_graphs(token_fn=...)``) the decode graph carries its own bookkeeping: a
+  ``decode_advance`` node updates ids/positions/slots/context_lens/block_tables on the device and a
+  greedy-argmax node leaves the next tokens on the device, so a steady-state step costs the host one
+  graph replay, one [B] token read-back and at most one [B] int32 upload.
 
 Sequences are duck-typed: ``len(seq)``, ``seq.token_ids``, ``seq.num_cached_tokens``,
 ``seq.block_table`` (the reference's ``Sequence`` qualifies, engine/sequence.py:31).
@@ -231,10 +235,16 @@ class HotPathExecutor:
         return self._d_ids[:b], self._d_pos[:b]
 
     # ------------------------------------------------------------------ T5: CUDA graphs
-    def capture_graphs(self, batch_sizes: list[int] | None = None) -> list[int]:
+    def capture_graphs(self, batch_sizes: list[int] | None = None, *,
+                       token_fn: Callable[[torch.Tensor, torch.Tensor], None] | None = None,
+                       capture: bool = True) -> list[int]:
         """Capture ``model(input_ids, positions)`` for the decode ladder, largest first (:823-920).
 
         Must run on every rank (the reference captures on rank 0 only, model_runner.py:113-115).
+        ``token_fn(hidden[bs, hidden], next_tokens[bs] int64)`` — when given, each graph becomes a
+        self-contained decode step: ``decode_advance`` -> model -> ``token_fn`` (see ``begin_decode``).
+        ``capture=False`` only allocates the persistent buffers; ``step_decode`` then runs the same three
+        stages eagerly (``enforce_eager``).
         """
         if self.model is None or self.device.type != "cuda":
             raise RuntimeError("CUDA graphs need a CUDA device and a model")
@@ -252,10 +262,23 @@ class HotPathExecutor:
             "block_tables": torch.zeros(max_bs, mb, dtype=torch.int32, device=dev),
             "outputs": torch.zeros(max_bs, self.hidden_size, dtype=self.dtype, device=dev),
             "workspace": torch.empty(max(ws, 1), dtype=torch.float32, device=dev),
+            "next_tokens": torch.zeros(max_bs, dtype=torch.int64, device=dev),
+            "appends": torch.full((max_bs,), -1, dtype=torch.int32, device=dev),
         }
         self.graph_bs = sorted(sizes)
+        self._token_fn = token_fn
         gv = self.graph_vars
-        for bs in reversed(self.graph_bs):
+        if token_fn is not None:
+            self.graph_vars["block_tables"].fill_(-1)
+
+        def body(bs: int) -> None:
+            if token_fn is not None:
+                self._advance(bs)
+            gv["outputs"][:bs].copy_(self.model(gv["input_ids"][:bs], gv["positions"][:bs]))
+            if token_fn is not None:
+                token_fn(gv["outputs"][:bs], gv["next_tokens"][:bs])
+
+        for bs in reversed(self.graph_bs if capture else []):
             self._set_context(
                 is_prefill=False, slot_mapping=gv["slot_mapping"][:bs], context_lens=gv["context_lens"][:bs],
                 block_tables=gv["block_tables"][:bs], decode_num_splits=self.graph_splits[bs],
@@ -265,19 +288,89 @@ class HotPathExecutor:
                 side = torch.cuda.Stream(device=dev)
                 side.wait_stream(torch.cuda.current_stream(dev))
                 with torch.cuda.stream(side), torch.inference_mode():
-                    gv["outputs"][:bs].copy_(self.model(gv["input_ids"][:bs], gv["positions"][:bs]))  # warm-up
+                    body(bs)  # warm-up
                 torch.cuda.current_stream(dev).wait_stream(side)
                 torch.cuda.synchronize(dev)
                 graph = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(graph, pool=self.graph_pool), torch.inference_mode():
-                    gv["outputs"][:bs].copy_(self.model(gv["input_ids"][:bs], gv["positions"][:bs]))
+                    body(bs)
                 if self.graph_pool is None:
                     self.graph_pool = graph.pool()
                 self.graphs[bs] = graph
             finally:
                 self._reset_context()
         torch.cuda.synchronize(dev)
+        if token_fn is not None:  # the warm-up passes advanced nothing (context_lens == 0) but leave a clean slate
+            gv["context_lens"].zero_()
+            gv["slot_mapping"].fill_(-1)
         return self.graph_bs
+
+    # ------------------------------------------------------------------ device-resident decode loop
+    def _advance(self, bs: int) -> None:
+        gv = self.graph_vars
+        ops.decode_advance(gv["next_tokens"][:bs], gv["appends"][:bs], gv["input_ids"][:bs], gv["positions"][:bs],
+                           gv["slot_mapping"][:bs], gv["context_lens"][:bs], gv["block_tables"][:bs],
+                           self.num_blocks, self.block_size)
+
+    def begin_decode(self, seqs: Seq[Any]) -> int:
+        """Load the persistent decode state of ``seqs`` (each already holding its newest token) into the
+        graph buffers: block tables as of now, ``context_lens = len-1`` and ``next_tokens = last token``
+        — the state ``decode_advance`` turns into exactly what ``_prepare_decode_input`` (:551-617)
+        would build for this step.  Rows beyond ``len(seqs)`` of the bucket become padding.  Returns the
+        graph bucket.  Call again whenever the set (or order) of running sequences changes."""
+        if not self.graph_vars or getattr(self, "_token_fn", None) is None:
+            raise RuntimeError("begin_decode needs capture_graphs(token_fn=...)")
+        b = len(seqs)
+        bs = next((x for x in self.graph_bs if x >= b), None)
+        if bs is None:
+            raise ValueError(f"batch {b} exceeds the largest captured graph ({self.graph_bs[-1] if self.graph_bs else 0})")
+        mb = self.max_blocks_per_seq
+        gv = self.graph_vars
+        lens = np.fromiter((len(s) for s in seqs), dtype=np.int64, count=b)
+        last = np.fromiter((s.token_ids[-1] for s in seqs), dtype=np.int64, count=b)
+        table = np.full((bs, mb), -1, dtype=np.int32)
+        for i, s in enumerate(seqs):
+            if len(s.block_table) > mb:
+                raise ValueError(f"sequence needs {len(s.block_table)} blocks, max_model_len allows {mb}")
+            table[i, : len(s.block_table)] = s.block_table
+        ctx = np.zeros(bs, dtype=np.int32)
+        ctx[:b] = lens - 1
+        tok = np.zeros(bs, dtype=np.int64)
+        tok[:b] = last
+        gv["block_tables"][:bs].copy_(self._to_device(table, torch.int32))
+        gv["context_lens"][:bs].copy_(self._to_device(ctx, torch.int32))
+        gv["next_tokens"][:bs].copy_(self._to_device(tok, torch.int64))
+        gv["appends"][:bs].fill_(-1)
+        self._loop_b, self._loop_bs = b, bs
+        self._h_app = self._host(bs, torch.int32)
+        return bs
+
+    @torch.inference_mode()
+    def step_decode(self, appends: dict[int, int] | None = None) -> torch.Tensor:
+        """One decode step of the loop opened by ``begin_decode``.  ``appends`` maps row -> physical block
+        id for the sequences whose newest token opened a block (BlockManager.may_append, len % BS == 1).
+        Returns the device vector of the ``b`` tokens picked by ``token_fn``; hidden states of the step
+        are in ``graph_vars['outputs'][:b]``."""
+        b, bs = self._loop_b, self._loop_bs
+        gv = self.graph_vars
+        if appends:
+            self._h_app.fill_(-1)
+            view = self._h_app.numpy()
+            for row, block in appends.items():
+                view[row] = block
+            gv["appends"][:bs].copy_(self._h_app, non_blocking=True)
+        if bs in self.graphs:
+            self.graphs[bs].replay()
+        else:  # eager twin (enforce_eager)
+            self._set_context(is_prefill=False, slot_mapping=gv["slot_mapping"][:bs], context_lens=gv["context_lens"][:bs],
+                              block_tables=gv["block_tables"][:bs])
+            try:
+                self._advance(bs)
+                gv["outputs"][:bs].copy_(self.model(gv["input_ids"][:bs], gv["positions"][:bs]))
+                self._token_fn(gv["outputs"][:bs], gv["next_tokens"][:bs])
+            finally:
+                self._reset_context()
+        return gv["next_tokens"][:b]
 
     def replay_decode(self, input_ids: torch.Tensor, positions: torch.Tensor) -> torch.Tensor | None:
         """Replay protocol of ``_execute_with_cuda_graph`` (:728-774); ``None`` if no graph fits."""
@@ -287,14 +380,21 @@ class HotPathExecutor:
             return None
         gv = self.graph_vars
         ctx = self._get_context()
-        gv["input_ids"][:b] = input_ids
-        gv["positions"][:b] = positions
-        gv["slot_mapping"].fill_(-1)
-        gv["slot_mapping"][:b] = ctx.slot_mapping
-        gv["context_lens"].zero_()
-        gv["context_lens"][:b] = ctx.context_lens
         width = ctx.block_tables.size(1)
         gv["block_tables"][:b, :width] = ctx.block_tables  # stale columns persist beyond `width` (:766-768)
+        gv["context_lens"].zero_()
+        if getattr(self, "_token_fn", None) is not None:
+            # self-advancing graph: hand it the state *before* this step; its first node rebuilds
+            # ids/positions/slots/context_lens from it (identical to what prepare_decode staged)
+            gv["next_tokens"][:b] = input_ids
+            gv["context_lens"][:b] = ctx.context_lens - 1
+            gv["appends"].fill_(-1)
+        else:
+            gv["input_ids"][:b] = input_ids
+            gv["positions"][:b] = positions
+            gv["slot_mapping"].fill_(-1)
+            gv["slot_mapping"][:b] = ctx.slot_mapping
+            gv["context_lens"][:b] = ctx.context_lens
         self.graphs[bs].replay()
         return gv["outputs"][:b]
 

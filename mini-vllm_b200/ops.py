@@ -10,6 +10,8 @@ Reference call sites (relative to the reference repository):
   paged_decode_attention     attention.py:439-447, page_attention.py:35-133
   prefill_varlen_attention   attention.py:396-433, :467-504
   qk_norm_rope_store         qwen_base.py:181-186 + attention.py:228-243 (caller-side fusion)
+  decode_advance             inference_executor.py:551-617, :651-688, :751-768 (device-side metadata)
+  greedy_argmax              sampling/sampler.py:104-106, :118-130 (temperature == 0)
 """
 
 from __future__ import annotations
@@ -375,6 +377,103 @@ def prefill_varlen_attention(
     if out_cast is not None:
         out_cast.copy_(out)
         return out_cast
+    return out
+
+
+# ---------------------------------------------------------------------------
+# device-side decode bookkeeping
+# ---------------------------------------------------------------------------
+
+
+def decode_advance(
+    next_tokens: torch.Tensor,
+    appends: torch.Tensor,
+    input_ids: torch.Tensor,
+    positions: torch.Tensor,
+    slot_mapping: torch.Tensor,
+    context_lens: torch.Tensor,
+    block_tables: torch.Tensor,
+    num_blocks: int,
+    block_size: int = 64,
+) -> None:
+    """Advance the persistent decode metadata by one token, in place, on the device.
+
+    What ``_prepare_decode_input`` + ``_prepare_block_tables_decode`` + the graph-buffer refill
+    (inference_executor.py:551-617, :651-688, :751-768) recompute on the host every step:
+    ``input_ids = next_tokens``, ``positions = len-1``, ``context_lens = len``,
+    ``slot = block_tables[(len-1)//BS]*BS + (len-1)%BS`` after writing ``appends[b]`` (a block id or -1)
+    into column ``(len-1)//BS``.  Rows with ``context_lens <= 0`` are padding.  ``appends`` is reset to -1.
+    """
+    _require_cuda(next_tokens, appends, input_ids, positions, slot_mapping, context_lens, block_tables)
+    b = context_lens.numel()
+    for name, t, dt in (("next_tokens", next_tokens, torch.int64), ("appends", appends, torch.int32),
+                        ("input_ids", input_ids, torch.int64), ("positions", positions, torch.int64),
+                        ("slot_mapping", slot_mapping, torch.int32), ("context_lens", context_lens, torch.int32)):
+        if t.dtype != dt or t.dim() != 1 or t.numel() != b or not t.is_contiguous():
+            raise ValueError(f"decode_advance: {name} must be a contiguous {dt} vector of {b} rows, "
+                             f"got {t.dtype} {tuple(t.shape)}")
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.size(0) != b:
+        raise ValueError(f"decode_advance: block_tables must be int32 [{b}, max_blocks], got "
+                         f"{block_tables.dtype} {tuple(block_tables.shape)}")
+    if block_tables.size(1) > 0 and block_tables.stride(1) != 1:
+        raise ValueError("decode_advance: block_tables rows must be dense")
+    if b == 0:
+        return
+    mb = block_tables.size(1)
+    stride = block_tables.stride(0) if b > 1 else max(mb, block_tables.stride(0))
+    rc = _native.lib().mvb200_decode_advance(
+        next_tokens.data_ptr(), appends.data_ptr(), input_ids.data_ptr(), positions.data_ptr(),
+        slot_mapping.data_ptr(), context_lens.data_ptr(), block_tables.data_ptr(), stride,
+        b, mb, block_size, num_blocks, _stream(),
+    )
+    _native.check(rc, "mvb200_decode_advance")
+
+
+def greedy_argmax_workspace_numel(rows: int, vocab: int) -> int:
+    """int64 elements of scratch ``greedy_argmax`` needs for ``rows x vocab`` logits."""
+    return (int(_native.lib().mvb200_greedy_argmax_workspace_bytes(rows, vocab)) + 7) // 8
+
+
+def greedy_argmax(
+    logits: torch.Tensor,
+    out: torch.Tensor | None = None,
+    *,
+    out_value: torch.Tensor | None = None,
+    index_offset: int = 0,
+    workspace: torch.Tensor | None = None,
+) -> torch.Tensor:
+    """``index_offset + argmax(logits, dim=-1)`` as int64 — the sampler's temperature == 0 branch
+    (sampling/sampler.py:104-106).  Ties go to the lowest index, NaN is the maximum (torch.argmax).
+    ``out_value`` (fp32 ``[rows]``) receives the winning logit; ``workspace`` (int64) must be passed
+    under CUDA-graph capture when the caller wants no allocation inside the graph."""
+    _require_cuda(logits, out, out_value, workspace)
+    if logits.dim() != 2:
+        raise ValueError(f"greedy_argmax: expected [rows, vocab] logits, got {tuple(logits.shape)}")
+    rows, vocab = logits.shape
+    if vocab == 0:
+        raise ValueError("greedy_argmax: empty vocabulary")
+    if logits.stride(1) != 1:
+        logits = logits.contiguous()
+    if out is None:
+        out = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    elif out.dtype != torch.int64 or out.numel() != rows or not out.is_contiguous():
+        raise ValueError("greedy_argmax: out must be a contiguous int64 vector with one entry per row")
+    if out_value is not None and (out_value.dtype != torch.float32 or out_value.numel() != rows
+                                  or not out_value.is_contiguous()):
+        raise ValueError("greedy_argmax: out_value must be a contiguous float32 vector with one entry per row")
+    if rows == 0:
+        return out
+    need = greedy_argmax_workspace_numel(rows, vocab)
+    if workspace is None:
+        workspace = torch.empty(max(need, 1), dtype=torch.int64, device=logits.device)
+    elif workspace.dtype != torch.int64 or workspace.numel() < need:
+        raise ValueError(f"greedy_argmax: workspace must be int64 with at least {need} elements")
+    rc = _native.lib().mvb200_greedy_argmax(
+        logits.data_ptr(), logits.stride(0) if rows > 1 else max(vocab, logits.stride(0)), rows, vocab,
+        _code(logits.dtype), workspace.data_ptr(), workspace.numel() * 8, out.data_ptr(),
+        out_value.data_ptr() if out_value is not None else None, index_offset, _stream(),
+    )
+    _native.check(rc, "mvb200_greedy_argmax")
     return out
 
 

@@ -93,7 +93,8 @@ def main():
             "metric": f"{cfg.name} end-to-end decode tokens/s", "value": best["decode_tokens"] / best["decode_s"],
             "unit": "tokens/s", "n_gpus": world, "parallelism": f"tp{world}", "dtype": "bf16", "data": "synthetic, random-init weights",
             "config": {"model": cfg.name, "sequences": args.seqs, "prompt_tokens": args.prompt, "prefix_cached_tokens": args.cached,
-                       "new_tokens": args.new_tokens, "cuda_graph": not args.eager, "max_model_len": args.max_model_len},
+                       "new_tokens": args.new_tokens, "cuda_graph": not args.eager, "max_model_len": args.max_model_len,
+                       "decode_bookkeeping": "device (decode_advance + greedy_argmax in the graph)" if eng.device_loop else "host (prepare_decode every step)"},
             "decode_ms_per_step": best["decode_s"] / max(best["decode_steps"], 1) * 1e3,
             "prefill_s": best["prefill_s"], "prefill_new_tokens": new_prefill, "prefill_tokens_per_s": new_prefill / best["prefill_s"],
             "prefix_hit_tokens": best["hit_tokens"], "engine_init_s": t_init,
