@@ -150,6 +150,10 @@ class Engine:
         torch.manual_seed(seed + rank)
         self.model.init_weights(init, seed)
         self.model.eval()
+        if tp > 1 and self.device.type == "cuda" and os.environ.get("MVB200_HARNESS_NCCL", "0") in ("", "0"):
+            import torch.distributed as dist
+
+            self.model.enable_peer_allreduce(max_num_seqs, group=dist.new_group(backend="gloo"))
         self.exe = HotPathExecutor(
             self.model, num_layers=cfg.num_layers, num_kv_heads=cfg.num_kv_heads // tp, num_heads=cfg.num_heads // tp,
             head_dim=cfg.head_dim, hidden_size=cfg.hidden_size, dtype=dtype, device=self.device,

@@ -109,18 +109,28 @@ class DecoderLayer(nn.Module):
             self.q_norm = self.k_norm = None
         self.rotary = rotary  # shared cos/sin tables
         self.attn = attention_cls(self.h, self.d, self.d ** -0.5, self.kvh)
+        self.comm = [None]  # shared one-element box, filled by QwenLM.enable_peer_allreduce
         self.fused_rope = os.environ.get("MVB200_HARNESS_UNFUSED", "0") in ("", "0")
 
-    def _norm(self, x, weight, residual):
+    def _norm(self, x, weight, residual, reduce=False):
+        """RMSNorm with residual; ``reduce``: ``x`` is this rank's partial sum of a row-parallel GEMM and is
+        all-reduced first (linear.py:316-319) — for decode-size messages by the fused peer kernel."""
+        if reduce and self.tp > 1:
+            comm = self.comm[0]
+            if comm is not None and x.is_cuda and residual is not None and comm.fits(x):
+                return comm.allreduce_add_rms_norm(x, weight, self.cfg.rms_eps, residual)
+            dist.all_reduce(x)
         if self.fused_rope and x.is_cuda:  # harness/csrc/fused_elementwise.cu
             return fused.add_rms_norm(x, weight, self.cfg.rms_eps, residual)
         if residual is None:
             return rms_norm(x, weight, self.cfg.rms_eps)[0], x
         return rms_norm(x, weight, self.cfg.rms_eps, residual)
 
-    def forward(self, positions, x, residual):
+    def forward(self, positions, x, residual, pending_reduce=False):
+        """``x`` arrives as the previous layer's un-reduced ``down_proj`` output when ``pending_reduce``;
+        this layer's own ``down_proj`` output is returned un-reduced (the next norm reduces it)."""
         cfg = self.cfg
-        x, residual = self._norm(x, self.in_norm, residual)
+        x, residual = self._norm(x, self.in_norm, residual, reduce=pending_reduce)
         n = x.size(0)
         qkv = F.linear(x, self.qkv_w, self.qkv_b)
         q, k, v = qkv.split([self.h * self.d, self.kvh * self.d, self.kvh * self.d], dim=-1)
@@ -136,19 +146,14 @@ class DecoderLayer(nn.Module):
             q, k = self.rotary(positions, q, k)
             o = self.attn(q, k, v).reshape(n, self.h * self.d)
         o = F.linear(o, self.o_w)
-        if self.tp > 1:
-            dist.all_reduce(o)
-        x, residual = self._norm(o, self.post_norm, residual)
+        x, residual = self._norm(o, self.post_norm, residual, reduce=True)
         gu = F.linear(x, self.gate_up_w)
         if self.fused_rope and gu.is_cuda:
             act = fused.silu_mul(gu)
         else:
             g, u = gu.chunk(2, dim=-1)
             act = F.silu(g) * u
-        x = F.linear(act, self.down_w)
-        if self.tp > 1:
-            dist.all_reduce(x)
-        return x, residual
+        return F.linear(act, self.down_w), residual
 
 
 class QwenLM(nn.Module):
@@ -164,12 +169,24 @@ class QwenLM(nn.Module):
     def forward(self, input_ids, positions):
         x = F.embedding(input_ids, self.embed)
         residual = None
+        for i, layer in enumerate(self.layers):
+            x, residual = layer(positions, x, residual, pending_reduce=i > 0)
+        return self.layers[-1]._norm(x, self.final_norm, residual, reduce=True)[0]
+
+    def enable_peer_allreduce(self, max_rows: int, group=None):
+        """TP > 1 on CUDA: route the decode-size all-reduce + add + RMSNorm through the one-shot NVLink
+        peer kernel (minivllm_b200.comm).  Collective: call on every rank."""
+        from minivllm_b200.comm import PeerAllReduce
+
+        if self.tp == 1:
+            return None
+        nbytes = max_rows * self.cfg.hidden_size * self.embed.element_size()
+        comm = PeerAllReduce(self.rank, self.tp, nbytes, group=group, device=self.embed.device)
+        box = self.layers[0].comm
+        box[0] = comm
         for layer in self.layers:
-            x, residual = layer(positions, x, residual)
-        if x.is_cuda and self.layers[0].fused_rope:
-            return fused.add_rms_norm(x, self.final_norm, self.cfg.rms_eps, residual)[0]
-        x, _ = rms_norm(x, self.final_norm, self.cfg.rms_eps, residual)
-        return x
+            layer.comm = box
+        return comm
 
     def compute_logits(self, hidden):
         """Full-vocabulary logits (TP=1) — used by parity tests."""

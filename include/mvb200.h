@@ -186,6 +186,43 @@ MVB200_API int mvb200_greedy_argmax(const void* logits, int64_t row_stride, int3
                           int32_t dtype, void* workspace, size_t workspace_bytes,
                           int64_t* out_index, float* out_value, int64_t index_offset, void* stream);
 
+/*
+ * Peer all-reduce fused with residual add + RMSNorm.
+ * Replaces, for decode-size messages, dist.all_reduce in RowParallelLinear.forward
+ * (models/layers/linear.py:314-319) and the RMSNorm.forward(x, residual) that follows it
+ * (models/layers/layernorm.py:81-105):
+ *   s = T( sum over ranks (rank order, fp32) of x_rank )            -- the all-reduce result, model dtype
+ *   if residual: r = float(s) + float(residual); residual = T(r)    else r = float(s)
+ *   y = weight ? T( r * (1/sqrt(mean(r^2) + eps)) * float(weight) ) : T(r)
+ * Every rank calls it with the same rows/hidden in the same order; every rank gets identical y/residual.
+ *
+ * Buffers (per rank, cudaMalloc'ed by mvb200_peer_alloc so they can be exported over CUDA IPC):
+ *   data : 2 * world * slot_bytes      (receive slots, double-buffered by call parity)
+ *   flags: mvb200_peer_flag_bytes()    (zero-initialised; [source rank][CTA] epochs)
+ *   epoch: mvb200_peer_epoch_bytes()   (zero-initialised, local only)
+ * data_ptrs[i] / flag_ptrs[i] are rank i's buffers as mapped into THIS process (own pointers at
+ * index `rank`; peers through mvb200_peer_export -> mvb200_peer_open).  rows*hidden*sizeof(T) <= slot_bytes,
+ * hidden*sizeof(T) a multiple of 16 and <= 16384.  No host sync, no allocation: CUDA-Graph capturable.
+ * Grid = min(rows, max_ctas or mvb200_peer_max_ctas()) CTAs, CTA c owning rows c, c+grid, ...; max_ctas
+ * (0 = library default) must be the same on every rank and for every call on a communicator.
+ * A peer that never arrives trips a device-side timeout (trap) after ~20 s instead of hanging the GPU.
+ */
+MVB200_API int mvb200_peer_flag_bytes(void);
+MVB200_API int mvb200_peer_epoch_bytes(void);
+MVB200_API int mvb200_peer_max_ctas(void);
+MVB200_API int mvb200_peer_alloc(size_t bytes, void** ptr);          /* cudaMalloc + zero */
+MVB200_API int mvb200_peer_free(void* ptr);
+MVB200_API int mvb200_peer_export(void* ptr, void* handle64);        /* cudaIpcGetMemHandle, 64 bytes */
+MVB200_API int mvb200_peer_open(const void* handle64, void** ptr);   /* cudaIpcOpenMemHandle */
+MVB200_API int mvb200_peer_close(void* ptr);
+MVB200_API int mvb200_peer_allreduce_add_rms_norm(void* const* data_ptrs, void* const* flag_ptrs, void* epoch,
+                          int64_t slot_bytes, int32_t rank, int32_t world,
+                          const void* x, int64_t x_row_stride,
+                          void* residual, int64_t residual_row_stride,
+                          const void* weight, void* y, int64_t y_row_stride,
+                          int32_t rows, int32_t hidden, float eps, int32_t dtype, int32_t max_ctas,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

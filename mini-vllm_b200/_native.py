@@ -64,6 +64,20 @@ SIGNATURES = {
         [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_size_t,
          c_void_p, c_void_p, c_int64, c_void_p],
     ),
+    "mvb200_peer_flag_bytes": (c_int32, []),
+    "mvb200_peer_epoch_bytes": (c_int32, []),
+    "mvb200_peer_max_ctas": (c_int32, []),
+    "mvb200_peer_alloc": (c_int32, [c_size_t, c_void_p]),
+    "mvb200_peer_free": (c_int32, [c_void_p]),
+    "mvb200_peer_export": (c_int32, [c_void_p, c_void_p]),
+    "mvb200_peer_open": (c_int32, [c_void_p, c_void_p]),
+    "mvb200_peer_close": (c_int32, [c_void_p]),
+    "mvb200_peer_allreduce_add_rms_norm": (
+        c_int32,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
+         c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
+         c_int32, c_int32, c_float, c_int32, c_int32, c_void_p],
+    ),
 }
 
 

@@ -14,6 +14,7 @@ SOURCES = [
     "store_kvcache.cu",
     "qk_rope_store.cu",
     "decode_meta.cu",
+    "peer_allreduce.cu",
     "paged_decode.cu",
     "prefill_generic.cu",
     "prefill_tcgen05.cu",

@@ -1,0 +1,133 @@
+"""One-shot all-reduce over NVLink peer memory, fused with the residual add + RMSNorm that follow it.
+
+Caller-side fusion of SURVEY.md 8(f) rank 3: replaces ``dist.all_reduce`` after the row-parallel
+``o_proj`` / ``down_proj`` (reference models/layers/linear.py:314-319) plus the next
+``RMSNorm.forward(x, residual)`` (models/layers/layernorm.py:81-105) for decode-size messages.  The kernel
+and its contract are in ``csrc/peer_allreduce.cu`` / ``include/mvb200.h``; this module only owns the
+buffers and the one-time handle exchange (``torch.distributed`` is the plumbing, CUDA IPC the transport).
+Larger messages (prefill) stay on NCCL: check ``fits()``.
+"""
+
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from . import _native
+from .ops import _code, _require_cuda, _stream
+
+
+class PeerAllReduce:
+    """Per-rank endpoint.  Build one per process with ``PeerAllReduce(rank, world, max_bytes, group=...)``
+    (handles travel through ``all_gather_object``) or ``PeerAllReduce.local_group`` for ``world`` endpoints
+    inside one process (tests on a single GPU: the kernel only needs peer *pointers*)."""
+
+    def __init__(self, rank: int, world: int, max_bytes: int, *, group=None, device=None, max_ctas: int = 0,
+                 _defer: bool = False):
+        lib = _native.lib()
+        if not 1 <= world <= 8:
+            raise ValueError(f"PeerAllReduce supports 1..8 ranks, got {world}")
+        self.rank, self.world = rank, world
+        self.max_ctas = int(max_ctas)  # 0: library default; identical on every rank
+        self.device = torch.device(device if device is not None else ("cuda", torch.cuda.current_device()))
+        self.slot_bytes = (int(max_bytes) + 255) // 256 * 256
+        self._lib = lib
+        self._opened: list[int] = []
+        with torch.cuda.device(self.device):
+            self._data = self._alloc(2 * world * self.slot_bytes)
+            self._flags = self._alloc(lib.mvb200_peer_flag_bytes())
+            self._epoch = self._alloc(lib.mvb200_peer_epoch_bytes())
+        self.data_ptrs = (ctypes.c_void_p * 8)()
+        self.flag_ptrs = (ctypes.c_void_p * 8)()
+        self.data_ptrs[rank], self.flag_ptrs[rank] = self._data, self._flags
+        if _defer:
+            return
+        if world > 1:
+            import torch.distributed as dist
+
+            mine = (self._export(self._data), self._export(self._flags))
+            everyone: list = [None] * world
+            dist.all_gather_object(everyone, mine, group=group)
+            with torch.cuda.device(self.device):
+                for r, (hd, hf) in enumerate(everyone):
+                    if r != rank:
+                        self.data_ptrs[r], self.flag_ptrs[r] = self._open(hd), self._open(hf)
+            dist.barrier(group=group)
+
+    # ---- construction helpers -------------------------------------------------------------------
+    @classmethod
+    def local_group(cls, world: int, max_bytes: int, device=None, max_ctas: int = 32) -> list["PeerAllReduce"]:
+        """``world`` endpoints on one device.  Their kernels wait for each other, so all of their CTAs must
+        be co-resident on that one GPU: ``max_ctas`` caps the grid (32 x 8 ranks fits a B200 several times)."""
+        eps = [cls(r, world, max_bytes, device=device, max_ctas=max_ctas, _defer=True) for r in range(world)]
+        for a in eps:
+            for b in eps:
+                a.data_ptrs[b.rank], a.flag_ptrs[b.rank] = b._data, b._flags
+        return eps
+
+    def _alloc(self, nbytes: int) -> int:
+        p = ctypes.c_void_p()
+        _native.check(self._lib.mvb200_peer_alloc(nbytes, ctypes.byref(p)), "mvb200_peer_alloc")
+        return p.value
+
+    def _export(self, ptr: int) -> bytes:
+        buf = ctypes.create_string_buffer(64)
+        _native.check(self._lib.mvb200_peer_export(ptr, buf), "mvb200_peer_export")
+        return buf.raw
+
+    def _open(self, handle: bytes) -> int:
+        p = ctypes.c_void_p()
+        _native.check(self._lib.mvb200_peer_open(handle, ctypes.byref(p)), "mvb200_peer_open")
+        self._opened.append(p.value)
+        return p.value
+
+    def close(self) -> None:
+        for p in self._opened:
+            self._lib.mvb200_peer_close(p)
+        self._opened = []
+        for name in ("_data", "_flags", "_epoch"):
+            p = getattr(self, name, None)
+            if p:
+                self._lib.mvb200_peer_free(p)
+                setattr(self, name, None)
+
+    # ---- the op ---------------------------------------------------------------------------------
+    def fits(self, x: torch.Tensor) -> bool:
+        row = x.size(-1) * x.element_size()
+        return x.dim() == 2 and x.numel() * x.element_size() <= self.slot_bytes and row % 16 == 0 and row <= 16384
+
+    def allreduce_add_rms_norm(self, x: torch.Tensor, weight: torch.Tensor | None, eps: float,
+                               residual: torch.Tensor | None = None, out: torch.Tensor | None = None):
+        """``y, residual`` of ``RMSNorm(all_reduce(x), residual)``; ``residual`` is updated in place.
+        ``weight=None``: no normalisation (``y = all_reduce(x) [+ residual]``)."""
+        _require_cuda(x, weight, residual, out)
+        if x.dim() != 2 or x.stride(1) != 1:
+            raise ValueError(f"peer all-reduce expects a [rows, hidden] tensor with dense rows, got {tuple(x.shape)}")
+        rows, hidden = x.shape
+        if not self.fits(x):
+            raise ValueError(f"message of {x.numel() * x.element_size()} bytes does not fit the {self.slot_bytes}-byte slots "
+                             "(or the row is not a multiple of 16 bytes / exceeds 16 KiB): use NCCL for this size")
+        for name, t in (("weight", weight), ("residual", residual), ("out", out)):
+            if t is not None and t.dtype != x.dtype:
+                raise ValueError(f"{name} dtype {t.dtype} != x dtype {x.dtype}")
+        if weight is not None and (weight.numel() != hidden or not weight.is_contiguous()):
+            raise ValueError("weight must be a contiguous [hidden] vector")
+        if residual is not None and (residual.shape != x.shape or residual.stride(1) != 1):
+            raise ValueError("residual must match x and have dense rows")
+        if out is None:
+            out = torch.empty((rows, hidden), dtype=x.dtype, device=x.device)
+        elif out.shape != x.shape or out.stride(1) != 1:
+            raise ValueError("out must match x and have dense rows")
+        rs = lambda t: t.stride(0) if rows > 1 else hidden  # noqa: E731
+        rc = self._lib.mvb200_peer_allreduce_add_rms_norm(
+            self.data_ptrs, self.flag_ptrs, self._epoch, self.slot_bytes, self.rank, self.world,
+            x.data_ptr(), rs(x), residual.data_ptr() if residual is not None else None,
+            rs(residual) if residual is not None else 0, weight.data_ptr() if weight is not None else None,
+            out.data_ptr(), rs(out), rows, hidden, float(eps), _code(x.dtype), self.max_ctas, _stream(),
+        )
+        _native.check(rc, "mvb200_peer_allreduce_add_rms_norm")
+        return out, residual
+
+    def all_reduce(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+        return self.allreduce_add_rms_norm(x, None, 0.0, None, out)[0]

@@ -23,7 +23,7 @@
 namespace mvb200 {
 
 constexpr int kMaxPeers = 8;
-constexpr int kMaxCtas = 64;     // flag slots per source rank
+constexpr int kMaxCtas = 256;    // flag slots per source rank (one CTA per row up to 256 rows)
 constexpr int kArThreads = 256;
 constexpr int kMaxChunks = 4;    // 16-byte chunks per thread per row: hidden*sizeof(T) <= 256*16*4 = 16 KiB
 
@@ -123,9 +123,11 @@ peer_allreduce_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __r
   const int nchunk = hidden / N;  // 16-byte chunks per row
   const int64_t row_bytes = (int64_t)hidden * sizeof(T);
 
-  if (tid == 0) s_epoch = comm.epoch[cta] + 1;  // local bookkeeping: safe before the dependency wait
-  pdl_wait();  // x comes from the GEMM before; residual from the norm before that
+  // x comes from the GEMM before, residual from the norm before that, and epoch[] from the previous
+  // peer all-reduce (which may be the kernel right before this one): nothing is read before the wait.
+  pdl_wait();
   pdl_launch_dependents();
+  if (tid == 0) s_epoch = comm.epoch[cta] + 1;
   __syncthreads();
   const uint32_t epoch = s_epoch;
   const int64_t parity_off = (int64_t)(epoch & 1) * comm.world * comm.slot_bytes;
@@ -287,7 +289,8 @@ int mvb200_peer_allreduce_add_rms_norm(void* const* data_ptrs, void* const* flag
                                        int64_t slot_bytes, int32_t rank, int32_t world, const void* x,
                                        int64_t x_row_stride, void* residual, int64_t residual_row_stride,
                                        const void* weight, void* y, int64_t y_row_stride, int32_t rows,
-                                       int32_t hidden, float eps, int32_t dtype, void* stream) {
+                                       int32_t hidden, float eps, int32_t dtype, int32_t max_ctas,
+                                       void* stream) {
   using namespace mvb200;
   if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world)
     return fail(MVB200_EINVAL, "peer_allreduce: bad rank/world (%d/%d, at most %d peers)", rank, world, kMaxPeers);
@@ -317,7 +320,8 @@ int mvb200_peer_allreduce_add_rms_norm(void* const* data_ptrs, void* const* flag
   comm.slot_bytes = slot_bytes;
   comm.rank = rank;
   comm.world = world;
-  const int32_t ctas = rows < kMaxCtas ? rows : kMaxCtas;
+  const int32_t cap = (max_ctas > 0 && max_ctas < kMaxCtas) ? max_ctas : kMaxCtas;  // same on every rank
+  const int32_t ctas = rows < cap ? rows : cap;
   note_kernel("peer_allreduce");
   cudaStream_t s = (cudaStream_t)stream;
   switch (dtype) {

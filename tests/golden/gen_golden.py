@@ -589,9 +589,58 @@ def gen_qkrope():
     save("qkrope", **out)
 
 
+# ---------------------------------------------------------------------------
+# caller side: all-reduce after the row-parallel GEMM, then RMSNorm with residual
+# ---------------------------------------------------------------------------
+
+
+def gen_arnorm():
+    """``RowParallelLinear.forward``'s ``dist.all_reduce(y)`` (linear.py:314-319) followed by the
+    reference's own ``RMSNorm.forward(x, residual)`` (layernorm.py:81-131).  The collective is a SUM in
+    the model dtype: recorded here as the in-dtype elementwise accumulation over ranks (what gloo does on
+    CPU; for world 2 every implementation gives T(a+b) exactly)."""
+    from minivllm.models.layers.layernorm import RMSNorm
+
+    out = {}
+    cases = [
+        # name, world, rows, hidden, dtype, residual?, norm?
+        ("tp2_bf16", 2, 8, 2560, torch.bfloat16, True, True),
+        ("tp2_bf16_first", 2, 5, 1024, torch.bfloat16, False, True),
+        ("tp4_bf16", 4, 3, 3584, torch.bfloat16, True, True),
+        ("tp8_f16", 8, 2, 1024, torch.float16, True, True),
+        ("tp2_f32", 2, 4, 256, torch.float32, True, True),
+        ("tp2_bf16_plain", 2, 6, 512, torch.bfloat16, False, False),
+    ]
+    for idx, (name, world, rows, hidden, dt, has_res, has_norm) in enumerate(cases):
+        g = torch.Generator().manual_seed(900 + idx)
+        xs = [randn(g, rows, hidden, dtype=dt) for _ in range(world)]
+        total = xs[0].clone()
+        for x in xs[1:]:
+            total += x
+        residual = randn(g, rows, hidden, dtype=dt) if has_res else None
+        if has_norm:
+            norm = RMSNorm(hidden, eps=1e-6)
+            norm.weight.data = (1.0 + 0.1 * randn(g, hidden)).to(dt)
+            y, new_res = norm(total, residual)
+            out[f"{name}.weight"] = to_np(norm.weight.data)
+        else:
+            y, new_res = total, None
+        for r, x in enumerate(xs):
+            out[f"{name}.x{r}"] = to_np(x)
+        if has_res:
+            out[f"{name}.residual_in"] = to_np(residual)
+            out[f"{name}.residual_out"] = to_np(new_res)
+        out[f"{name}.sum"] = to_np(total)
+        out[f"{name}.y"] = to_np(y)
+        out[f"{name}.meta"] = np.array([world, rows, hidden, int(has_res), int(has_norm)])
+        out[f"{name}.dtype"] = np.array(dtype_name(dt))
+    out["cases"] = np.array([c[0] for c in cases])
+    save("arnorm", **out)
+
+
 if __name__ == "__main__":
     print("generating golden vectors from", REFERENCE)
     only = set(sys.argv[1:])
-    for fn in (gen_store, gen_decode, gen_prefill, gen_layer, gen_metadata, gen_engine, gen_qkrope):
+    for fn in (gen_store, gen_decode, gen_prefill, gen_layer, gen_metadata, gen_engine, gen_qkrope, gen_arnorm):
         if not only or fn.__name__[4:] in only:
             fn()
