@@ -148,7 +148,20 @@ peer_allreduce_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __r
   // 2. publish + wait.  A peer can start call n+1 (overwriting parity (n+1)&1) only after it saw my flag
   //    for call n+1... which I set after finishing call n, so parity n&1 is not rewritten before call n+2,
   //    and a peer enters call n+2 only after I published call n+1, i.e. after I finished reading call n.
-  __threadfence_system();
+  //    The release store is cumulative over the CTA barrier: every thread's pushes happen-before it.
+  //    While the flags travel, prefetch what phase 3 needs from local memory (first row's residual, weight).
+  uint4 res_pf[kMaxChunks], w_pf[kMaxChunks];
+#pragma unroll
+  for (int it = 0; it < kMaxChunks; ++it) {
+    const int c = tid + it * kArThreads;
+    res_pf[it] = make_uint4(0, 0, 0, 0);
+    w_pf[it] = make_uint4(0, 0, 0, 0);
+    if (c < nchunk) {
+      if (residual && cta < rows)
+        res_pf[it] = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(residual + (int64_t)cta * rs) + (int64_t)c * 16);
+      if (weight) w_pf[it] = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(weight) + (int64_t)c * 16);
+    }
+  }
   __syncthreads();
   if (tid < comm.world) {
     st_release_sys(comm.flags[tid] + comm.rank * kMaxCtas + cta, epoch);
@@ -188,7 +201,7 @@ peer_allreduce_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __r
         if (residual) {
           uint4* rp = reinterpret_cast<uint4*>(reinterpret_cast<char*>(residual + (int64_t)r * rs) + (int64_t)c * 16);
           float f[N];
-          Pack<T>::unpack(*rp, f);
+          Pack<T>::unpack(r == cta ? res_pf[it] : *rp, f);
 #pragma unroll
           for (int e = 0; e < N; ++e) vals[it][e] += f[e];
           summed = Pack<T>::pack(vals[it]);
@@ -215,7 +228,7 @@ peer_allreduce_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __r
       const int c = tid + it * kArThreads;
       if (c < nchunk) {
         float w[N], o[N];
-        Pack<T>::unpack(*reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(weight) + (int64_t)c * 16), w);
+        Pack<T>::unpack(w_pf[it], w);
 #pragma unroll
         for (int e = 0; e < N; ++e) o[e] = __fmul_rn(__fmul_rn(vals[it][e], inv), w[e]);
         *reinterpret_cast<uint4*>(reinterpret_cast<char*>(y + (int64_t)r * ys) + (int64_t)c * 16) = Pack<T>::pack(o);
