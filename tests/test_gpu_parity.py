@@ -220,6 +220,8 @@ def _random_paged(device, batch, ctxs, kvh, d, bs, dtype, seed, extra_blocks=8):
         ("cfg2_qwen3_0.6b", 256, 2048, 16, 8),
         ("cfg4_qwen2_7b_32k", 2, 32768, 28, 4),
         ("cfg5_qwen2_72b_rank", 512, 1024, 8, 1),
+        ("cfg2_tp8_rank", 256, 2048, 2, 1),
+        ("cfg4_tp4_rank", 1, 32768, 7, 1),
     ],
 )
 def test_decode_full_size_against_oracle_samples(m, cuda_device, name, batch, ctx, h, kvh):
