@@ -2,7 +2,7 @@
 """Run under torchrun on N GPUs of one node: parity and latency of the fused peer all-reduce + add + RMSNorm
 (mini-vllm_b200/comm.py) against NCCL all_reduce followed by the harness add_rms_norm kernel.
 
-    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tools/peer_allreduce_check.py
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tests/mp_peer_allreduce_check.py
 
 Rank 0 prints one JSON line per shape and finally PEER_ALLREDUCE_OK.  The oracle is used here only as the
 checker (this tool is test infrastructure)."""

@@ -4,7 +4,7 @@ CPU part pins oracle/allreduce_oracle.py on tests/golden/arnorm.npz (the referen
 an in-dtype sum over ranks).  GPU part (``-m gpu``): the CUDA kernel through the C ABI.  On a single GPU
 the ``world`` endpoints live in one process and run concurrently on ``world`` streams — the kernel only
 sees peer pointers, so the flag/epoch protocol, the double buffering and the arithmetic are exactly what
-runs across processes over NVLink (that transport itself is exercised by tools/peer_allreduce_check.py
+runs across processes over NVLink (that transport itself is exercised by tests/mp_peer_allreduce_check.py
 under torchrun, and by the test at the bottom when the box has two GPUs).
 """
 
@@ -242,6 +242,6 @@ def test_two_processes_over_cuda_ipc(cuda_device):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
-           "--master-port", "29731", os.path.join(ROOT, "tools", "peer_allreduce_check.py")]
+           "--master-port", "29731", os.path.join(ROOT, "tests", "mp_peer_allreduce_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert r.returncode == 0 and "PEER_ALLREDUCE_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

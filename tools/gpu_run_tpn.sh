@@ -4,7 +4,7 @@ set -u
 N=${1:-4}
 mkdir -p gpurun_out
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
-timeout 300 $TR --master-port 29611 tools/peer_allreduce_check.py > gpurun_out/peer_check_tp$N.txt 2> gpurun_out/peer_check_tp$N.err; echo "peer check exit $?"; cat gpurun_out/peer_check_tp$N.txt; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/peer_check_tp$N.err | tail -5
+timeout 300 $TR --master-port 29611 tests/mp_peer_allreduce_check.py > gpurun_out/peer_check_tp$N.txt 2> gpurun_out/peer_check_tp$N.err; echo "peer check exit $?"; cat gpurun_out/peer_check_tp$N.txt; grep -v "^\*\|OMP_NUM\|^$" gpurun_out/peer_check_tp$N.err | tail -5
 timeout 600 $TR --master-port 29612 tools/e2e_bench.py --model qwen3-4b --seqs 8 --prompt 2048 --cached 1024 --new-tokens 256 --watchdog 500 > gpurun_out/e2e_cfg3_tp${N}_peer.json 2> gpurun_out/e2e_cfg3_tp${N}_peer.err; echo "e2e cfg3 peer exit $?"
 MVB200_HARNESS_NCCL=1 timeout 600 $TR --master-port 29613 tools/e2e_bench.py --model qwen3-4b --seqs 8 --prompt 2048 --cached 1024 --new-tokens 256 --watchdog 500 > gpurun_out/e2e_cfg3_tp${N}_nccl.json 2> gpurun_out/e2e_cfg3_tp${N}_nccl.err; echo "e2e cfg3 nccl exit $?"
 timeout 600 $TR --master-port 29614 tools/e2e_bench.py --model qwen3-0.6b --seqs 256 --prompt 2048 --cached 0 --new-tokens 64 --repeat 1 --watchdog 500 > gpurun_out/e2e_cfg2_tp${N}_peer.json 2> gpurun_out/e2e_cfg2_tp${N}_peer.err; echo "e2e cfg2 peer exit $?"
