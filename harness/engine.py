@@ -89,6 +89,8 @@ class BlockPool:
         if len(self.free) < seq.num_blocks:
             raise ValueError(f"No free blocks available for allocation: need {seq.num_blocks}, have {len(self.free)}")
         h = -1
+        seq._fresh = []  # blocks whose hash this call registered (their KV is not computed yet)
+        hits0, misses0 = self.hits, self.misses
         for i in range(seq.num_blocks):
             toks = seq.block(i)
             h = self.compute_hash(toks, h) if len(toks) == self.block_size else -1
@@ -106,7 +108,9 @@ class BlockPool:
                 self.hash_of[bid], self.tokens_of[bid] = h, (toks if h != -1 else None)
                 if h != -1:
                     self.by_hash[h] = bid
+                    seq._fresh.append(bid)
             seq.block_table.append(bid)
+        seq._counted = (self.hits - hits0, self.misses - misses0)
 
     def may_append(self, seq: Seq):
         n, bs = len(seq), self.block_size
@@ -124,7 +128,17 @@ class BlockPool:
             self.by_hash[h] = last
         return None
 
-    def deallocate(self, seq: Seq):
+    def deallocate(self, seq: Seq, computed: bool = True):
+        """``computed=False``: the sequence is put back before its prefill ran, so the hashes ``allocate``
+        registered for it must not be hit by anybody (their blocks hold no KV yet)."""
+        if not computed:
+            dh, dm = getattr(seq, "_counted", (0, 0))
+            self.hits, self.misses = self.hits - dh, self.misses - dm
+            for bid in getattr(seq, "_fresh", []):
+                h = self.hash_of[bid]
+                if self.by_hash.get(h) == bid:
+                    del self.by_hash[h]
+                self.hash_of[bid], self.tokens_of[bid] = -1, None
         for bid in reversed(seq.block_table):
             self.ref[bid] -= 1
             if self.ref[bid] == 0:
@@ -221,7 +235,7 @@ class Engine:
                 self.pool.allocate(s)
                 need = len(s) - s.num_cached_tokens
                 if batch and ntok + need > self.max_num_batched_tokens:
-                    self.pool.deallocate(s)
+                    self.pool.deallocate(s, computed=False)
                     break
                 waiting.popleft()
                 batch.append(s)

@@ -42,6 +42,10 @@ PRESETS = {
     "qwen3-0.6b": ModelConfig("Qwen3-0.6B", 151936, 1024, 28, 16, 8, 128, 3072),
     "qwen3-4b": ModelConfig("Qwen3-4B", 151936, 2560, 36, 32, 8, 128, 9728),
     "qwen2-7b": ModelConfig("Qwen2-7B", 152064, 3584, 28, 28, 4, 128, 18944, qkv_bias=True, tie_embeddings=False),
+    "qwen2-72b": ModelConfig("Qwen2-72B", 152064, 8192, 80, 64, 8, 128, 29568, qkv_bias=True, tie_embeddings=False),
+    # what ONE rank of Qwen2-72B at TP=8 computes (heads, kv heads, MLP and vocabulary divided by 8): lets a single
+    # GPU run cfg5's per-rank engine workload; only the hidden-size all-reduces are missing
+    "qwen2-72b-rank8": ModelConfig("Qwen2-72B (one TP8 rank)", 19008, 8192, 80, 8, 1, 128, 3696, qkv_bias=True, tie_embeddings=False),
     # tiny fp32-able configs for parity tests (head_dim stays 128 so the fast kernels are exercised in bf16)
     "tiny-qwen3": ModelConfig("tiny-qwen3", 512, 256, 2, 4, 2, 128, 512, max_position=2048, tie_embeddings=False),
     "tiny-qwen2": ModelConfig("tiny-qwen2", 512, 256, 2, 4, 2, 64, 512, qkv_bias=True, max_position=2048, tie_embeddings=False),
@@ -180,7 +184,9 @@ class QwenLM(nn.Module):
 
         if self.tp == 1:
             return None
-        nbytes = max_rows * self.cfg.hidden_size * self.embed.element_size()
+        # one-shot wins while the message is latency-bound; from ~2 MiB on NCCL's bandwidth algorithms catch up
+        # (tests/mp_peer_allreduce_check.py on 8 x B200: 512 KiB 19 vs 33 us, 4 MiB 63 vs 60 us)
+        nbytes = min(max_rows * self.cfg.hidden_size * self.embed.element_size(), 2 << 20)
         comm = PeerAllReduce(self.rank, self.tp, nbytes, group=group, device=self.embed.device)
         box = self.layers[0].comm
         box[0] = comm

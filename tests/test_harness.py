@@ -87,6 +87,21 @@ def test_prefix_hits_do_not_change_generation_on_cpu():
 
 
 # ------------------------------------------------------------------------------------------------
+def test_prefill_batch_split_does_not_fake_prefix_hits():
+    """A sequence put back because the token budget is full must not leave hashes of never-computed blocks
+    behind (it would 'hit' them when it is scheduled again and skip its own prefill)."""
+    from tests.oracle_attention import OracleAttention
+
+    g = torch.Generator().manual_seed(21)
+    prompts = [torch.randint(10, 500, (n,), generator=g).tolist() for n in (200, 150, 130, 70)]
+    whole = _engine("tiny-qwen3", "cpu", torch.float32, OracleAttention)
+    want, _ = whole.generate(prompts, 6)
+    split = _engine("tiny-qwen3", "cpu", torch.float32, OracleAttention, max_num_batched_tokens=256)
+    got, _ = split.generate(prompts, 6)
+    assert split.stats["prefix_hits"] == 0 and whole.stats["prefix_hits"] == 0
+    assert got == want
+
+
 # GPU: the same harness around the CUDA layer
 # ------------------------------------------------------------------------------------------------
 
