@@ -122,7 +122,8 @@ class DecoderLayer(nn.Module):
         if reduce and self.tp > 1:
             comm = self.comm[0]
             if comm is not None and x.is_cuda and residual is not None and comm.fits(x):
-                return comm.allreduce_add_rms_norm(x, weight, self.cfg.rms_eps, residual)
+                # the residual stream is consumed by these calls only: leave it row-sharded (two-shot sizes)
+                return comm.allreduce_add_rms_norm(x, weight, self.cfg.rms_eps, residual, gather_residual=False)
             dist.all_reduce(x)
         if self.fused_rope and x.is_cuda:  # harness/csrc/fused_elementwise.cu
             return fused.add_rms_norm(x, weight, self.cfg.rms_eps, residual)
@@ -184,9 +185,8 @@ class QwenLM(nn.Module):
 
         if self.tp == 1:
             return None
-        # one-shot wins while the message is latency-bound; from ~2 MiB on NCCL's bandwidth algorithms catch up
-        # (tests/mp_peer_allreduce_check.py on 8 x B200: 512 KiB 19 vs 33 us, 4 MiB 63 vs 60 us)
-        nbytes = min(max_rows * self.cfg.hidden_size * self.embed.element_size(), 2 << 20)
+        # decode-size messages only (one-shot up to 128 KiB, two-shot above); prefill stays on NCCL
+        nbytes = min(max_rows * self.cfg.hidden_size * self.embed.element_size(), 16 << 20)
         comm = PeerAllReduce(self.rank, self.tp, nbytes, group=group, device=self.embed.device)
         box = self.layers[0].comm
         box[0] = comm

@@ -197,12 +197,17 @@ MVB200_API int mvb200_greedy_argmax(const void* logits, int64_t row_stride, int3
  * Every rank calls it with the same rows/hidden in the same order; every rank gets identical y/residual.
  *
  * Buffers (per rank, cudaMalloc'ed by mvb200_peer_alloc so they can be exported over CUDA IPC):
- *   data : 2 * world * slot_bytes      (receive slots, double-buffered by call parity)
+ *   data : 2 * (world + 2) * slot_bytes  (per call parity: world partial slots, one Y and one R region)
  *   flags: mvb200_peer_flag_bytes()    (zero-initialised; [source rank][CTA] epochs)
  *   epoch: mvb200_peer_epoch_bytes()   (zero-initialised, local only)
  * data_ptrs[i] / flag_ptrs[i] are rank i's buffers as mapped into THIS process (own pointers at
  * index `rank`; peers through mvb200_peer_export -> mvb200_peer_open).  rows*hidden*sizeof(T) <= slot_bytes,
  * hidden*sizeof(T) a multiple of 16 and <= 16384.  No host sync, no allocation: CUDA-Graph capturable.
+ * algo 1 = one-shot (every rank pushes its whole partial to every peer; latency-bound sizes),
+ * algo 2 = two-shot (row r is reduced and normalised by rank (r % cap) % world only, which then pushes the
+ * finished row to everybody: (world-1)/world of the message per direction).  With algo 2 and
+ * gather_residual == 0 the residual stays row-sharded: a rank updates only the rows it owns.
+ * All ranks must pass the same algo / gather_residual / max_ctas for a given call.
  * Grid = min(rows, max_ctas or mvb200_peer_max_ctas()) CTAs, CTA c owning rows c, c+grid, ...; max_ctas
  * (0 = library default) must be the same on every rank and for every call on a communicator.
  * A peer that never arrives trips a device-side timeout (trap) after ~20 s instead of hanging the GPU.
@@ -221,7 +226,7 @@ MVB200_API int mvb200_peer_allreduce_add_rms_norm(void* const* data_ptrs, void* 
                           void* residual, int64_t residual_row_stride,
                           const void* weight, void* y, int64_t y_row_stride,
                           int32_t rows, int32_t hidden, float eps, int32_t dtype, int32_t max_ctas,
-                          void* stream);
+                          int32_t algo, int32_t gather_residual, void* stream);
 
 #ifdef __cplusplus
 }

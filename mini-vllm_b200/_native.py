@@ -76,7 +76,7 @@ SIGNATURES = {
         c_int32,
         [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
          c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
-         c_int32, c_int32, c_float, c_int32, c_int32, c_void_p],
+         c_int32, c_int32, c_float, c_int32, c_int32, c_int32, c_int32, c_void_p],
     ),
 }
 

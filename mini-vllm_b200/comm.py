@@ -35,7 +35,7 @@ class PeerAllReduce:
         self._lib = lib
         self._opened: list[int] = []
         with torch.cuda.device(self.device):
-            self._data = self._alloc(2 * world * self.slot_bytes)
+            self._data = self._alloc(2 * (world + 2) * self.slot_bytes)
             self._flags = self._alloc(lib.mvb200_peer_flag_bytes())
             self._epoch = self._alloc(lib.mvb200_peer_epoch_bytes())
         self.data_ptrs = (ctypes.c_void_p * 8)()
@@ -97,10 +97,19 @@ class PeerAllReduce:
         row = x.size(-1) * x.element_size()
         return x.dim() == 2 and x.numel() * x.element_size() <= self.slot_bytes and row % 16 == 0 and row <= 16384
 
+    #: messages up to this many bytes use the one-shot kernel, larger ones the two-shot kernel
+    #: (tests/mp_peer_allreduce_check.py prints both; the crossover sits near 128-256 KiB on 4-8 GPUs)
+    ONE_SHOT_MAX_BYTES = 128 * 1024
+
     def allreduce_add_rms_norm(self, x: torch.Tensor, weight: torch.Tensor | None, eps: float,
-                               residual: torch.Tensor | None = None, out: torch.Tensor | None = None):
+                               residual: torch.Tensor | None = None, out: torch.Tensor | None = None, *,
+                               algo: int | None = None, gather_residual: bool = True):
         """``y, residual`` of ``RMSNorm(all_reduce(x), residual)``; ``residual`` is updated in place.
-        ``weight=None``: no normalisation (``y = all_reduce(x) [+ residual]``)."""
+        ``weight=None``: no normalisation (``y = all_reduce(x) [+ residual]``).
+        ``algo``: 1 one-shot, 2 two-shot, ``None`` picks by size.  ``gather_residual=False`` (two-shot only)
+        leaves the residual row-sharded: this rank then updates only the rows it owns, which is all a
+        decoder needs when every consumer of the residual is one of these calls.  Every rank must make the
+        same choice."""
         _require_cuda(x, weight, residual, out)
         if x.dim() != 2 or x.stride(1) != 1:
             raise ValueError(f"peer all-reduce expects a [rows, hidden] tensor with dense rows, got {tuple(x.shape)}")
@@ -119,15 +128,18 @@ class PeerAllReduce:
             out = torch.empty((rows, hidden), dtype=x.dtype, device=x.device)
         elif out.shape != x.shape or out.stride(1) != 1:
             raise ValueError("out must match x and have dense rows")
+        if algo is None:
+            algo = 1 if x.numel() * x.element_size() <= self.ONE_SHOT_MAX_BYTES or self.world == 1 else 2
         rs = lambda t: t.stride(0) if rows > 1 else hidden  # noqa: E731
         rc = self._lib.mvb200_peer_allreduce_add_rms_norm(
             self.data_ptrs, self.flag_ptrs, self._epoch, self.slot_bytes, self.rank, self.world,
             x.data_ptr(), rs(x), residual.data_ptr() if residual is not None else None,
             rs(residual) if residual is not None else 0, weight.data_ptr() if weight is not None else None,
-            out.data_ptr(), rs(out), rows, hidden, float(eps), _code(x.dtype), self.max_ctas, _stream(),
+            out.data_ptr(), rs(out), rows, hidden, float(eps), _code(x.dtype), self.max_ctas,
+            int(algo), 1 if gather_residual else 0, _stream(),
         )
         _native.check(rc, "mvb200_peer_allreduce_add_rms_norm")
         return out, residual
 
-    def all_reduce(self, x: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
-        return self.allreduce_add_rms_norm(x, None, 0.0, None, out)[0]
+    def all_reduce(self, x: torch.Tensor, out: torch.Tensor | None = None, algo: int | None = None) -> torch.Tensor:
+        return self.allreduce_add_rms_norm(x, None, 0.0, None, out, algo=algo)[0]

@@ -15,7 +15,8 @@
 //   3. sums the world_size slots from its own HBM/L2 in rank order in fp32 (every rank gets bit-identical
 //      results), rounds once to the model dtype (the all-reduce output), adds the residual, writes the new
 //      residual and the normalised row.
-// The epoch lives in device memory and is bumped by the kernel itself, so the launch is CUDA-Graph
+// (A two-shot variant for larger messages — reduce-scatter by rows, all-gather of the finished rows — is
+// further down.)  The epoch lives in device memory and is bumped by the kernel itself, so the launch is CUDA-Graph
 // capturable; receive buffers are double-buffered by epoch parity (a rank can only be one call ahead of
 // a peer, see wait below).  Latency-bound by design: ~2 NVLink traversals per call.
 #include "common.cuh"
@@ -29,7 +30,7 @@ constexpr int kMaxChunks = 4;    // 16-byte chunks per thread per row: hidden*si
 
 struct PeerComm {
   char* data[kMaxPeers];          // receive buffers: [2 parities][world slots][slot_bytes]
-  uint32_t* flags[kMaxPeers];     // [world sources][kMaxCtas]
+  uint32_t* flags[kMaxPeers];     // [2 phases][kMaxPeers sources][kMaxCtas]
   uint32_t* epoch;                // local, [kMaxCtas]
   int64_t slot_bytes;
   int32_t rank, world;
@@ -107,7 +108,89 @@ struct Pack<__half> {
   }
 };
 
-// grid = G CTAs (G <= kMaxCtas, the same on every rank); CTA c owns rows c, c+G, ...
+// ---- shared pieces ---------------------------------------------------------------------------------
+// Spin until *flag has reached `epoch` (a peer may already be one call ahead).  A peer that never arrives
+// is a protocol or launch-order bug: trap after ~20 s of SM clocks instead of hanging the GPU.
+MVB_DEV void wait_flag(const uint32_t* flag, uint32_t epoch, int rank, int from, int cta, int phase) {
+  const long long t0 = clock64();
+  while ((int32_t)(ld_acquire_sys(flag) - epoch) < 0) {
+    if (clock64() - t0 > 40000000000LL) {
+      printf("mvb200: peer all-reduce timed out (rank %d waits for rank %d, cta %d, phase %d, epoch %u, saw %u)\n",
+             rank, from, cta, phase, epoch, ld_acquire_sys(flag));
+      __trap();
+    }
+  }
+}
+
+// One row, whole CTA: sum the `world` partials in rank order in fp32 (load(s, c) = 16-byte chunk c of rank s),
+// round once to T (what dist.all_reduce returns), add the residual (kept in fp32 for the norm, written back
+// rounded: layernorm.py:96-99), normalise.  emit(c, y16, res16) receives the packed outputs per chunk.
+template <typename T, typename Load, typename Emit>
+MVB_DEV void reduce_norm_row(Load load, Emit emit, int world, int nchunk, int hidden, float eps,
+                             const uint4* res_row /* this row's residual or null */,
+                             const uint4* res_pf /* prefetched residual chunks or null */, bool has_weight,
+                             const uint4* w_pf, float* red) {
+  constexpr int N = Pack<T>::N;
+  const int tid = threadIdx.x;
+  float vals[kMaxChunks][N];
+  float ss = 0.f;
+#pragma unroll
+  for (int it = 0; it < kMaxChunks; ++it) {
+    const int c = tid + it * kArThreads;
+    if (c < nchunk) {
+      float acc[N];
+#pragma unroll
+      for (int e = 0; e < N; ++e) acc[e] = 0.f;
+      for (int s = 0; s < world; ++s) {
+        float f[N];
+        Pack<T>::unpack(load(s, c), f);
+#pragma unroll
+        for (int e = 0; e < N; ++e) acc[e] += f[e];
+      }
+      uint4 summed = Pack<T>::pack(acc);
+      Pack<T>::unpack(summed, vals[it]);
+      if (res_row) {
+        float f[N];
+        Pack<T>::unpack(res_pf ? res_pf[it] : res_row[c], f);
+#pragma unroll
+        for (int e = 0; e < N; ++e) vals[it][e] += f[e];
+        summed = Pack<T>::pack(vals[it]);
+      }
+      if (!has_weight) emit(c, summed, summed);
+#pragma unroll
+      for (int e = 0; e < N; ++e) ss += vals[it][e] * vals[it][e];
+    }
+  }
+  if (!has_weight) return;  // uniform across the CTA
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  __syncthreads();  // red[] free again
+  if ((tid & 31) == 0) red[tid >> 5] = ss;
+  __syncthreads();
+  float tot = 0.f;
+#pragma unroll
+  for (int i = 0; i < kArThreads / 32; ++i) tot += red[i];
+  const float inv = 1.f / sqrtf(tot / (float)hidden + eps);
+#pragma unroll
+  for (int it = 0; it < kMaxChunks; ++it) {
+    const int c = tid + it * kArThreads;
+    if (c < nchunk) {
+      float w[N], o[N];
+      Pack<T>::unpack(w_pf[it], w);
+#pragma unroll
+      for (int e = 0; e < N; ++e) o[e] = __fmul_rn(__fmul_rn(vals[it][e], inv), w[e]);
+      emit(c, Pack<T>::pack(o), Pack<T>::pack(vals[it]));
+    }
+  }
+}
+
+MVB_DEV char* row_ptr(void* base, int64_t row, int64_t stride_bytes) {
+  return reinterpret_cast<char*>(base) + row * stride_bytes;
+}
+
+// ---- one-shot: every rank pushes everything to everybody ------------------------------------------
+// grid = G CTAs (the same on every rank); CTA c owns rows c, c+G, ... (row -> CTA is r % cap for every
+// row count, so a row keeps its CTA, and with it its epoch parity, from call to call).
 // x [rows, hidden] partial sums of this rank (row stride xs elements);
 // residual (nullable) [rows, hidden] updated in place; weight (nullable) [hidden];
 // y [rows, hidden]: weight ? RMSNorm(sum + residual) * weight : sum (+ residual).
@@ -130,7 +213,7 @@ peer_allreduce_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __r
   if (tid == 0) s_epoch = comm.epoch[cta] + 1;
   __syncthreads();
   const uint32_t epoch = s_epoch;
-  const int64_t parity_off = (int64_t)(epoch & 1) * comm.world * comm.slot_bytes;
+  const int64_t parity_off = (int64_t)(epoch & 1) * (comm.world + 2) * comm.slot_bytes;
 
   // 1. push my rows into slot [parity][rank] of every peer (self included: one code path, one sum order)
   for (int r = cta; r < rows; r += G) {
@@ -145,11 +228,10 @@ peer_allreduce_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __r
       }
     }
   }
-  // 2. publish + wait.  A peer can start call n+1 (overwriting parity (n+1)&1) only after it saw my flag
-  //    for call n+1... which I set after finishing call n, so parity n&1 is not rewritten before call n+2,
-  //    and a peer enters call n+2 only after I published call n+1, i.e. after I finished reading call n.
-  //    The release store is cumulative over the CTA barrier: every thread's pushes happen-before it.
-  //    While the flags travel, prefetch what phase 3 needs from local memory (first row's residual, weight).
+  // 2. publish + wait.  Completing call n+1 needs every peer's flag for n+1, which a peer publishes only
+  //    after it finished call n entirely (stream order): so parity n&1 is never rewritten (in call n+2)
+  //    while somebody still reads call n.  The release store is cumulative over the CTA barrier: every
+  //    thread's pushes happen-before it.  While the flags travel, prefetch what step 3 needs locally.
   uint4 res_pf[kMaxChunks], w_pf[kMaxChunks];
 #pragma unroll
   for (int it = 0; it < kMaxChunks; ++it) {
@@ -158,91 +240,149 @@ peer_allreduce_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __r
     w_pf[it] = make_uint4(0, 0, 0, 0);
     if (c < nchunk) {
       if (residual && cta < rows)
-        res_pf[it] = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(residual + (int64_t)cta * rs) + (int64_t)c * 16);
+        res_pf[it] = *reinterpret_cast<const uint4*>(row_ptr(residual, cta, rs * sizeof(T)) + (int64_t)c * 16);
       if (weight) w_pf[it] = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(weight) + (int64_t)c * 16);
     }
   }
   __syncthreads();
   if (tid < comm.world) {
     st_release_sys(comm.flags[tid] + comm.rank * kMaxCtas + cta, epoch);
-    const uint32_t* mine = comm.flags[comm.rank] + tid * kMaxCtas + cta;
-    const long long t0 = clock64();
-    while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-      if (clock64() - t0 > 40000000000LL) {  // ~20 s of SM clocks: a peer never arrived
-        printf("mvb200: peer all-reduce timed out (rank %d waits for rank %d, cta %d, epoch %u, saw %u)\n",
-               comm.rank, tid, cta, epoch, ld_acquire_sys(mine));
-        __trap();
-      }
-    }
+    wait_flag(comm.flags[comm.rank] + tid * kMaxCtas + cta, epoch, comm.rank, tid, cta, 1);
   }
   __syncthreads();
   if (tid == 0) comm.epoch[cta] = epoch;
 
-  // 3. reduce in rank order, round to T (the all-reduce result), add residual, normalise
+  // 3. reduce + residual + norm, all local
   const char* base = comm.data[comm.rank] + parity_off;
   for (int r = cta; r < rows; r += G) {
-    float vals[kMaxChunks][N];
-    float ss = 0.f;
-#pragma unroll
-    for (int it = 0; it < kMaxChunks; ++it) {
-      const int c = tid + it * kArThreads;
-      if (c < nchunk) {
-        float acc[N];
-#pragma unroll
-        for (int e = 0; e < N; ++e) acc[e] = 0.f;
-        for (int s = 0; s < comm.world; ++s) {
-          float f[N];
-          Pack<T>::unpack(ld_cg(base + s * comm.slot_bytes + r * row_bytes + (int64_t)c * 16), f);
-#pragma unroll
-          for (int e = 0; e < N; ++e) acc[e] += f[e];
-        }
-        uint4 summed = Pack<T>::pack(acc);  // dist.all_reduce returns the model dtype
-        Pack<T>::unpack(summed, vals[it]);
-        if (residual) {
-          uint4* rp = reinterpret_cast<uint4*>(reinterpret_cast<char*>(residual + (int64_t)r * rs) + (int64_t)c * 16);
-          float f[N];
-          Pack<T>::unpack(r == cta ? res_pf[it] : *rp, f);
-#pragma unroll
-          for (int e = 0; e < N; ++e) vals[it][e] += f[e];
-          summed = Pack<T>::pack(vals[it]);
-          *rp = summed;  // residual = (x + residual).to(dtype); the norm uses the fp32 value (layernorm.py:96-99)
-        }
-        if (!weight)
-          *reinterpret_cast<uint4*>(reinterpret_cast<char*>(y + (int64_t)r * ys) + (int64_t)c * 16) = summed;
-#pragma unroll
-        for (int e = 0; e < N; ++e) ss += vals[it][e] * vals[it][e];
-      }
-    }
-    if (!weight) continue;  // uniform across the CTA
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
-    __syncthreads();  // red[] free again
-    if ((tid & 31) == 0) red[tid >> 5] = ss;
-    __syncthreads();
-    float tot = 0.f;
-#pragma unroll
-    for (int i = 0; i < kArThreads / 32; ++i) tot += red[i];
-    const float inv = 1.f / sqrtf(tot / (float)hidden + eps);
-#pragma unroll
-    for (int it = 0; it < kMaxChunks; ++it) {
-      const int c = tid + it * kArThreads;
-      if (c < nchunk) {
-        float w[N], o[N];
-        Pack<T>::unpack(w_pf[it], w);
-#pragma unroll
-        for (int e = 0; e < N; ++e) o[e] = __fmul_rn(__fmul_rn(vals[it][e], inv), w[e]);
-        *reinterpret_cast<uint4*>(reinterpret_cast<char*>(y + (int64_t)r * ys) + (int64_t)c * 16) = Pack<T>::pack(o);
-      }
-    }
+    char* res_row = residual ? row_ptr(residual, r, rs * sizeof(T)) : nullptr;
+    char* y_row = row_ptr(y, r, ys * sizeof(T));
+    reduce_norm_row<T>(
+        [&](int s, int c) { return ld_cg(base + s * comm.slot_bytes + r * row_bytes + (int64_t)c * 16); },
+        [&](int c, const uint4& yv, const uint4& rv) {
+          *reinterpret_cast<uint4*>(y_row + (int64_t)c * 16) = yv;
+          if (res_row) *reinterpret_cast<uint4*>(res_row + (int64_t)c * 16) = rv;
+        },
+        comm.world, nchunk, hidden, eps, reinterpret_cast<const uint4*>(res_row), r == cta ? res_pf : nullptr,
+        weight != nullptr, w_pf, red);
   }
+}
+
+// ---- two-shot: reduce-scatter by rows, all-gather of the normalised rows ---------------------------
+// For messages past the latency-bound range.  CTA c of every rank handles rows c, c+G, ... (G a multiple
+// of world) and those rows are OWNED by rank c % world:
+//   non-owner: push my partial rows into the owner's slot [parity][rank]            (1/world of the
+//              message per peer instead of all of it), release flag1 on the owner, wait for the owner's
+//              flag2, copy the finished rows from my own Y (and R) region into y (and residual);
+//   owner:     wait flag1 of every peer, reduce (own partial straight from x) + residual + norm, write
+//              y/residual locally and push them into every peer's Y (/R) region, release flag2 everywhere.
+// Per rank and call: (world-1)/world of the message in, the same out (twice that when the residual is
+// gathered too) instead of (world-1) x the message with one-shot.  gather_residual == 0 leaves the residual
+// stream row-sharded: each rank keeps only the rows it owns up to date (enough for a decoder whose residual
+// is consumed by these kernels only; the first call of a forward pass starts from a replicated residual).
+template <typename T>
+__global__ void __launch_bounds__(kArThreads)
+peer_allreduce_twoshot_kernel(PeerComm comm, const T* __restrict__ x, int64_t xs, T* __restrict__ residual,
+                              int64_t rs, const T* __restrict__ weight, T* __restrict__ y, int64_t ys,
+                              int32_t rows, int32_t hidden, float eps, int32_t gather_residual) {
+  constexpr int N = Pack<T>::N;
+  __shared__ float red[kArThreads / 32];
+  __shared__ uint32_t s_epoch;
+  const int cta = blockIdx.x, G = gridDim.x, tid = threadIdx.x;
+  const int nchunk = hidden / N;
+  const int64_t row_bytes = (int64_t)hidden * sizeof(T);
+  const int owner = cta % comm.world;
+  const bool mine = owner == comm.rank;
+  const bool push_res = residual != nullptr && gather_residual != 0;
+
+  pdl_wait();
+  pdl_launch_dependents();
+  if (tid == 0) s_epoch = comm.epoch[cta] + 1;
+  __syncthreads();
+  const uint32_t epoch = s_epoch;
+  const int64_t parity_off = (int64_t)(epoch & 1) * (comm.world + 2) * comm.slot_bytes;
+  const int64_t y_off = parity_off + (int64_t)comm.world * comm.slot_bytes;  // Y region, R region follows
+
+  if (!mine) {
+    for (int r = cta; r < rows; r += G) {
+      const char* src = reinterpret_cast<const char*>(x + (int64_t)r * xs);
+      char* dst = comm.data[owner] + parity_off + comm.rank * comm.slot_bytes + r * row_bytes;
+      for (int c = tid; c < nchunk; c += kArThreads)
+        *reinterpret_cast<uint4*>(dst + (int64_t)c * 16) = *reinterpret_cast<const uint4*>(src + (int64_t)c * 16);
+    }
+    __syncthreads();
+    if (tid == 0) {
+      st_release_sys(comm.flags[owner] + comm.rank * kMaxCtas + cta, epoch);
+      wait_flag(comm.flags[comm.rank] + (kMaxPeers + owner) * kMaxCtas + cta, epoch, comm.rank, owner, cta, 2);
+    }
+    __syncthreads();
+    if (tid == 0) comm.epoch[cta] = epoch;
+    const char* ybase = comm.data[comm.rank] + y_off;
+    for (int r = cta; r < rows; r += G) {
+      for (int c = tid; c < nchunk; c += kArThreads) {
+        *reinterpret_cast<uint4*>(row_ptr(y, r, ys * sizeof(T)) + (int64_t)c * 16) =
+            ld_cg(ybase + r * row_bytes + (int64_t)c * 16);
+        if (push_res)
+          *reinterpret_cast<uint4*>(row_ptr(residual, r, rs * sizeof(T)) + (int64_t)c * 16) =
+              ld_cg(ybase + comm.slot_bytes + r * row_bytes + (int64_t)c * 16);
+      }
+    }
+    return;
+  }
+
+  // owner
+  uint4 w_pf[kMaxChunks];
+#pragma unroll
+  for (int it = 0; it < kMaxChunks; ++it) {
+    const int c = tid + it * kArThreads;
+    w_pf[it] = make_uint4(0, 0, 0, 0);
+    if (c < nchunk && weight)
+      w_pf[it] = *reinterpret_cast<const uint4*>(reinterpret_cast<const char*>(weight) + (int64_t)c * 16);
+  }
+  if (tid < comm.world && tid != comm.rank)
+    wait_flag(comm.flags[comm.rank] + tid * kMaxCtas + cta, epoch, comm.rank, tid, cta, 1);
+  __syncthreads();
+  const char* base = comm.data[comm.rank] + parity_off;
+  for (int r = cta; r < rows; r += G) {
+    const char* x_row = reinterpret_cast<const char*>(x + (int64_t)r * xs);
+    char* res_row = residual ? row_ptr(residual, r, rs * sizeof(T)) : nullptr;
+    char* y_row = row_ptr(y, r, ys * sizeof(T));
+    reduce_norm_row<T>(
+        [&](int s, int c) {
+          return s == comm.rank ? *reinterpret_cast<const uint4*>(x_row + (int64_t)c * 16)
+                                : ld_cg(base + s * comm.slot_bytes + r * row_bytes + (int64_t)c * 16);
+        },
+        [&](int c, const uint4& yv, const uint4& rv) {
+          *reinterpret_cast<uint4*>(y_row + (int64_t)c * 16) = yv;
+          if (res_row) *reinterpret_cast<uint4*>(res_row + (int64_t)c * 16) = rv;
+          const int64_t off = y_off + r * row_bytes + (int64_t)c * 16;
+#pragma unroll 1
+          for (int p = 1; p < comm.world; ++p) {
+            const int peer = (comm.rank + p) % comm.world;
+            *reinterpret_cast<uint4*>(comm.data[peer] + off) = yv;
+            if (push_res) *reinterpret_cast<uint4*>(comm.data[peer] + off + comm.slot_bytes) = rv;
+          }
+        },
+        comm.world, nchunk, hidden, eps, reinterpret_cast<const uint4*>(res_row), nullptr, weight != nullptr,
+        w_pf, red);
+  }
+  __syncthreads();
+  if (tid < comm.world && tid != comm.rank)
+    st_release_sys(comm.flags[tid] + (kMaxPeers + comm.rank) * kMaxCtas + cta, epoch);
+  if (tid == 0) comm.epoch[cta] = epoch;
 }
 
 template <typename T>
 static int launch_ar(const PeerComm& comm, const void* x, int64_t xs, void* residual, int64_t rs,
                      const void* weight, void* y, int64_t ys, int32_t rows, int32_t hidden, float eps,
-                     int32_t ctas, cudaStream_t s) {
-  cudaError_t e = launch_pdl(peer_allreduce_kernel<T>, dim3(ctas), dim3(kArThreads), 0, s, comm,
-                             (const T*)x, xs, (T*)residual, rs, (const T*)weight, (T*)y, ys, rows, hidden, eps);
+                     int32_t ctas, int32_t algo, int32_t gather_residual, cudaStream_t s) {
+  cudaError_t e;
+  if (algo == 2)
+    e = launch_pdl(peer_allreduce_twoshot_kernel<T>, dim3(ctas), dim3(kArThreads), 0, s, comm, (const T*)x, xs,
+                   (T*)residual, rs, (const T*)weight, (T*)y, ys, rows, hidden, eps, gather_residual);
+  else
+    e = launch_pdl(peer_allreduce_kernel<T>, dim3(ctas), dim3(kArThreads), 0, s, comm, (const T*)x, xs,
+                   (T*)residual, rs, (const T*)weight, (T*)y, ys, rows, hidden, eps);
   if (e != cudaSuccess) return fail(MVB200_ECUDA, "peer_allreduce: %s", cudaGetErrorString(e));
   return check_launch("peer_allreduce");
 }
@@ -251,7 +391,7 @@ static int launch_ar(const PeerComm& comm, const void* x, int64_t xs, void* resi
 
 extern "C" {
 
-int mvb200_peer_flag_bytes(void) { return mvb200::kMaxPeers * mvb200::kMaxCtas * (int)sizeof(uint32_t); }
+int mvb200_peer_flag_bytes(void) { return 2 * mvb200::kMaxPeers * mvb200::kMaxCtas * (int)sizeof(uint32_t); }
 int mvb200_peer_epoch_bytes(void) { return mvb200::kMaxCtas * (int)sizeof(uint32_t); }
 int mvb200_peer_max_ctas(void) { return mvb200::kMaxCtas; }
 
@@ -303,7 +443,7 @@ int mvb200_peer_allreduce_add_rms_norm(void* const* data_ptrs, void* const* flag
                                        int64_t x_row_stride, void* residual, int64_t residual_row_stride,
                                        const void* weight, void* y, int64_t y_row_stride, int32_t rows,
                                        int32_t hidden, float eps, int32_t dtype, int32_t max_ctas,
-                                       void* stream) {
+                                       int32_t algo, int32_t gather_residual, void* stream) {
   using namespace mvb200;
   if (world < 1 || world > kMaxPeers || rank < 0 || rank >= world)
     return fail(MVB200_EINVAL, "peer_allreduce: bad rank/world (%d/%d, at most %d peers)", rank, world, kMaxPeers);
@@ -333,17 +473,21 @@ int mvb200_peer_allreduce_add_rms_norm(void* const* data_ptrs, void* const* flag
   comm.slot_bytes = slot_bytes;
   comm.rank = rank;
   comm.world = world;
-  const int32_t cap = (max_ctas > 0 && max_ctas < kMaxCtas) ? max_ctas : kMaxCtas;  // same on every rank
-  const int32_t ctas = rows < cap ? rows : cap;
+  if (algo != 1 && algo != 2) return fail(MVB200_EINVAL, "peer_allreduce: algo must be 1 (one-shot) or 2 (two-shot)");
+  int32_t cap = (max_ctas > 0 && max_ctas < kMaxCtas) ? max_ctas : kMaxCtas;  // same on every rank
+  cap -= cap % world;  // row r is always handled by CTA r % cap, whose owner (two-shot) is rank (r % cap) % world
+  if (cap < world) return fail(MVB200_EINVAL, "peer_allreduce: max_ctas %d is smaller than the world size %d", max_ctas, world);
+  const int32_t want = algo == 2 ? (rows + world - 1) / world * world : rows;
+  const int32_t ctas = want < cap ? want : cap;
   note_kernel("peer_allreduce");
   cudaStream_t s = (cudaStream_t)stream;
   switch (dtype) {
     case MVB200_BF16:
-      return launch_ar<__nv_bfloat16>(comm, x, x_row_stride, residual, residual_row_stride, weight, y, y_row_stride, rows, hidden, eps, ctas, s);
+      return launch_ar<__nv_bfloat16>(comm, x, x_row_stride, residual, residual_row_stride, weight, y, y_row_stride, rows, hidden, eps, ctas, algo, gather_residual, s);
     case MVB200_F16:
-      return launch_ar<__half>(comm, x, x_row_stride, residual, residual_row_stride, weight, y, y_row_stride, rows, hidden, eps, ctas, s);
+      return launch_ar<__half>(comm, x, x_row_stride, residual, residual_row_stride, weight, y, y_row_stride, rows, hidden, eps, ctas, algo, gather_residual, s);
     default:
-      return launch_ar<float>(comm, x, x_row_stride, residual, residual_row_stride, weight, y, y_row_stride, rows, hidden, eps, ctas, s);
+      return launch_ar<float>(comm, x, x_row_stride, residual, residual_row_stride, weight, y, y_row_stride, rows, hidden, eps, ctas, algo, gather_residual, s);
   }
 }
 

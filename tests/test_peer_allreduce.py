@@ -83,7 +83,7 @@ def test_header_declares_peer_entry_points():
 
 
 # ------------------------------------------------------------------------------------------------ GPU
-def _run_group(eps, streams, xs, weight, eps_val, residuals, outs=None):
+def _run_group(eps, streams, xs, weight, eps_val, residuals, outs=None, **kw):
     """Launch every endpoint's kernel on its own stream (they wait for each other on the device)."""
     results = []
     cur = torch.cuda.current_stream()
@@ -92,7 +92,7 @@ def _run_group(eps, streams, xs, weight, eps_val, residuals, outs=None):
     for r, (ep, s) in enumerate(zip(eps, streams)):
         with torch.cuda.stream(s):
             results.append(ep.allreduce_add_rms_norm(xs[r], weight, eps_val, residuals[r] if residuals else None,
-                                                     outs[r] if outs else None))
+                                                     outs[r] if outs else None, **kw))
     for s in streams:
         cur.wait_stream(s)
     return results
@@ -106,8 +106,9 @@ def comm_mod():
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("algo", [1, 2])
 @pytest.mark.parametrize("name", CASES)
-def test_kernel_matches_oracle_and_golden(comm_mod, cuda_device, name):
+def test_kernel_matches_oracle_and_golden(comm_mod, cuda_device, name, algo):
     c = _case(name, cuda_device)
     world = c["world"]
     eps = comm_mod.PeerAllReduce.local_group(world, 64 * 1024, cuda_device)
@@ -115,7 +116,7 @@ def test_kernel_matches_oracle_and_golden(comm_mod, cuda_device, name):
     try:
         for rep in range(3):  # epochs 1..3: both parities, flag reuse
             residuals = [c["residual_in"].clone() for _ in range(world)] if c["residual_in"] is not None else None
-            res = _run_group(eps, streams, c["xs"], c["weight"], 1e-6, residuals)
+            res = _run_group(eps, streams, c["xs"], c["weight"], 1e-6, residuals, algo=algo)
             torch.cuda.synchronize()
             want_y, want_res = O.allreduce_add_rms_norm([x.cpu() for x in c["xs"]], None if c["weight"] is None else c["weight"].cpu(),
                                                         1e-6, None if c["residual_in"] is None else c["residual_in"].cpu())
@@ -154,7 +155,7 @@ def test_kernel_varying_rows_many_epochs(comm_mod, cuda_device, world):
             xs = [torch.randn(rows, hidden, generator=g).to(torch.bfloat16).to(cuda_device) for _ in range(world)]
             res0 = torch.randn(rows, hidden, generator=g).to(torch.bfloat16).to(cuda_device)
             residuals = [res0.clone() for _ in range(world)]
-            out = _run_group(eps, streams, xs, weight, 1e-6, residuals)
+            out = _run_group(eps, streams, xs, weight, 1e-6, residuals, algo=1 + (it * 7 // 3) % 2)  # mixes both kernels
             if it % 3 == 2:
                 torch.cuda.synchronize()  # otherwise back-to-back launches (programmatic dependent launch overlap)
             want_y, want_res = O.allreduce_add_rms_norm([x.cpu() for x in xs], weight.cpu(), 1e-6, res0.cpu())
@@ -173,6 +174,36 @@ def test_kernel_varying_rows_many_epochs(comm_mod, cuda_device, world):
         torch.cuda.synchronize()
         for y in ys:
             assert torch.equal(y.cpu(), O.all_reduce_sum([x.cpu() for x in xs]))
+    finally:
+        for ep in eps:
+            ep.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_twoshot_sharded_residual(comm_mod, cuda_device, world):
+    """gather_residual=False: y is complete everywhere, the residual is updated only on the rows a rank owns
+    (row r -> rank (r % cap) % world, cap = the CTA cap rounded down to a multiple of world)."""
+    rows, hidden, cap = 45, 1024, 32
+    eps = comm_mod.PeerAllReduce.local_group(world, rows * hidden * 2, cuda_device, max_ctas=cap)
+    streams = [torch.cuda.Stream(cuda_device) for _ in range(world)]
+    g = torch.Generator().manual_seed(40 + world)
+    weight = (1.0 + 0.1 * torch.randn(hidden, generator=g)).to(torch.bfloat16).to(cuda_device)
+    try:
+        for it in range(3):
+            xs = [torch.randn(rows, hidden, generator=g).to(torch.bfloat16).to(cuda_device) for _ in range(world)]
+            res0 = torch.randn(rows, hidden, generator=g).to(torch.bfloat16).to(cuda_device)
+            residuals = [res0.clone() for _ in range(world)]
+            out = _run_group(eps, streams, xs, weight, 1e-6, residuals, algo=2, gather_residual=False)
+            torch.cuda.synchronize()
+            want_y, want_res = O.allreduce_add_rms_norm([x.cpu() for x in xs], weight.cpu(), 1e-6, res0.cpu())
+            owner = (torch.arange(rows) % (cap - cap % world)) % world
+            for r in range(world):
+                assert torch.equal(out[r][0], out[0][0])
+                assert float(_ulps(out[r][0], want_y, "bf16").max()) <= 1.0
+                got = residuals[r].cpu()
+                assert torch.equal(got[owner == r], want_res[owner == r])
+                assert torch.equal(got[owner != r], res0.cpu()[owner != r])
     finally:
         for ep in eps:
             ep.close()
