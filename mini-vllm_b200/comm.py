@@ -98,8 +98,9 @@ class PeerAllReduce:
         return x.dim() == 2 and x.numel() * x.element_size() <= self.slot_bytes and row % 16 == 0 and row <= 16384
 
     #: messages up to this many bytes use the one-shot kernel, larger ones the two-shot kernel
-    #: (tests/mp_peer_allreduce_check.py prints both; the crossover sits near 128-256 KiB on 4-8 GPUs)
-    ONE_SHOT_MAX_BYTES = 128 * 1024
+    #: (tests/mp_peer_allreduce_check.py prints both; 8 x B200: equal at 512 KiB (19.4 vs 19.6 us), two-shot ahead
+    #: from there on: 4 MiB 62 vs 35 us, 8 MiB 115 vs 52 us; NCCL all_reduce + norm kernel: 33 / 60 / 79 us)
+    ONE_SHOT_MAX_BYTES = 1024 * 1024
 
     def allreduce_add_rms_norm(self, x: torch.Tensor, weight: torch.Tensor | None, eps: float,
                                residual: torch.Tensor | None = None, out: torch.Tensor | None = None, *,
