@@ -20,6 +20,8 @@
 //   y1 = T(x1*cos - x2*sin), y2 = T(x2*cos + x1*sin) on float(xn) halves, products rounded
 //   separately (no FMA contraction: __fmul_rn / __fadd_rn / __fsub_rn).
 // One warp per row; lane l owns element pairs (2p, 2p+1) of both halves for p = l, l+32, ...
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace mvb200 {
@@ -172,6 +174,150 @@ qk_rope_store_kernel(const RopeParams p) {
   }
 }
 
+// ---- vectorised path: 16-bit dtypes, head_dim 128, 16-byte aligned rows ---------------------------
+// The pair kernel above keeps one 256-byte row per warp in flight with 4-byte accesses; at prefill sizes
+// (cfg3: 8192 tokens x 48 rows) that is latency-bound at ~1.6 TB/s.  Here 8 lanes own a row (16 bytes of
+// each half per lane) and a warp works on 4 rows at a time: 1 KiB in flight per warp, 128-bit accesses.
+// Same arithmetic and rounding points; only the order of the 128-term sum inside mean() differs.
+template <typename T> struct Vec8;
+template <> struct Vec8<__nv_bfloat16> {
+  static MVB_DEV void unpack(const uint4& r, float* f) {
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { f[2 * i] = __uint_as_float(w[i] << 16); f[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u); }
+  }
+  static MVB_DEV uint4 pack(const float* f) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { __nv_bfloat162 v = __halves2bfloat162(__float2bfloat16_rn(f[2 * i]), __float2bfloat16_rn(f[2 * i + 1])); w[i] = *reinterpret_cast<uint32_t*>(&v); }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+template <> struct Vec8<__half> {
+  static MVB_DEV void unpack(const uint4& r, float* f) {
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { const float2 v = __half22float2(*reinterpret_cast<const __half2*>(&w[i])); f[2 * i] = v.x; f[2 * i + 1] = v.y; }
+  }
+  static MVB_DEV uint4 pack(const float* f) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { __half2 v = __halves2half2(__float2half_rn(f[2 * i]), __float2half_rn(f[2 * i + 1])); w[i] = *reinterpret_cast<uint32_t*>(&v); }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+qk_rope_store_vec_kernel(const RopeParams p) {
+  constexpr int D = 128, HALF = 64;
+  pdl_wait();
+  pdl_launch_dependents();
+  const int lane = threadIdx.x & 31;
+  const int li = lane & 7;       // 16-byte chunk of each half owned by this lane
+  const int rsub = lane >> 3;    // which of the warp's 4 rows
+  const int warps_per_cta = blockDim.x >> 5;
+  const int64_t warp0 = (int64_t)blockIdx.x * warps_per_cta + (threadIdx.x >> 5);
+  const int64_t warp_stride = (int64_t)gridDim.x * warps_per_cta;
+  const int rows_per_tok = p.H + 2 * p.KVH;
+  const int64_t groups = (p.total_rows + 3) >> 2;
+
+  for (int64_t grp = warp0; grp < groups; grp += warp_stride) {
+    const int64_t row = grp * 4 + rsub;
+    const bool valid = row < p.total_rows;
+    const int64_t tok = valid ? row / rows_per_tok : 0;
+    const int j = valid ? (int)(row - tok * rows_per_tok) : 0;
+    const bool is_q = j < p.H;
+    const bool is_k = !is_q && j < p.H + p.KVH;
+    const int head = is_q ? j : (is_k ? j - p.H : j - p.H - p.KVH);
+    int64_t slot = -1;
+    if (valid && !is_q && p.slots) {
+      slot = p.slots[tok];
+      if (slot >= p.num_slots) slot = -1;
+    }
+    const bool is_v = !is_q && !is_k;
+    const T* src = is_q ? static_cast<const T*>(p.q) + tok * p.q_stride + (int64_t)head * D
+                        : (is_k ? static_cast<const T*>(p.k) + tok * p.k_stride + (int64_t)head * D
+                                : static_cast<const T*>(p.v) + tok * p.v_stride + (int64_t)head * D);
+    uint4 ra = make_uint4(0, 0, 0, 0), rb = make_uint4(0, 0, 0, 0);
+    if (valid && !(is_v && slot < 0)) {
+      ra = *reinterpret_cast<const uint4*>(src + li * 8);
+      rb = *reinterpret_cast<const uint4*>(src + HALF + li * 8);
+    }
+    if (is_v) {  // plain copy into the cache (no shuffles below depend on these lanes' data)
+      if (valid && slot >= 0) {
+        T* dst = static_cast<T*>(p.v_cache) + (slot * p.KVH + head) * D;
+        *reinterpret_cast<uint4*>(dst + li * 8) = ra;
+        *reinterpret_cast<uint4*>(dst + HALF + li * 8) = rb;
+      }
+    }
+    float a[8], b[8];
+    Vec8<T>::unpack(ra, a);
+    Vec8<T>::unpack(rb, b);
+    const T* w = static_cast<const T*>(is_q ? p.q_weight : p.k_weight);
+    if (p.q_weight) {  // uniform: q and k weights come together; every lane takes part in the shuffles
+      float ss = 0.f;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ss += __fmul_rn(a[e], a[e]) + __fmul_rn(b[e], b[e]);
+#pragma unroll
+      for (int o = 4; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+      if (valid && !is_v) {
+        const float var = __fdiv_rn(ss, (float)D);
+        const float inv = __fdiv_rn(1.f, __fsqrt_rn(__fadd_rn(var, p.eps)));
+        float wa[8], wb[8];
+        Vec8<T>::unpack(*reinterpret_cast<const uint4*>(w + li * 8), wa);
+        Vec8<T>::unpack(*reinterpret_cast<const uint4*>(w + HALF + li * 8), wb);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          a[e] = __fmul_rn(__fmul_rn(a[e], inv), wa[e]);
+          b[e] = __fmul_rn(__fmul_rn(b[e], inv), wb[e]);
+        }
+        // RMSNorm's .to(orig_dtype), then back to fp32 for the rotation
+        Vec8<T>::unpack(Vec8<T>::pack(a), a);
+        Vec8<T>::unpack(Vec8<T>::pack(b), b);
+      }
+    }
+    if (!valid || is_v) continue;
+    int64_t pos = p.positions[tok];
+    pos = pos < 0 ? 0 : (pos >= p.max_pos ? p.max_pos - 1 : pos);
+    const float4* cs = reinterpret_cast<const float4*>(p.cos_cache + pos * HALF + li * 8);
+    const float4* sn = reinterpret_cast<const float4*>(p.sin_cache + pos * HALF + li * 8);
+    const float4 c0 = __ldg(cs), c1 = __ldg(cs + 1), s0 = __ldg(sn), s1 = __ldg(sn + 1);
+    const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+    const float sv[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+    float y1[8], y2[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      y1[e] = __fsub_rn(__fmul_rn(a[e], c[e]), __fmul_rn(b[e], sv[e]));
+      y2[e] = __fadd_rn(__fmul_rn(b[e], c[e]), __fmul_rn(a[e], sv[e]));
+    }
+    const uint4 o1 = Vec8<T>::pack(y1), o2 = Vec8<T>::pack(y2);
+    T* dst = is_q ? static_cast<T*>(p.q_out) + tok * p.qo_stride + (int64_t)head * D
+                  : (p.k_out ? static_cast<T*>(p.k_out) + tok * p.ko_stride + (int64_t)head * D : nullptr);
+    if (dst) {
+      *reinterpret_cast<uint4*>(dst + li * 8) = o1;
+      *reinterpret_cast<uint4*>(dst + HALF + li * 8) = o2;
+    }
+    if (is_k && slot >= 0) {
+      T* cdst = static_cast<T*>(p.k_cache) + (slot * p.KVH + head) * D;
+      *reinterpret_cast<uint4*>(cdst + li * 8) = o1;
+      *reinterpret_cast<uint4*>(cdst + HALF + li * 8) = o2;
+    }
+  }
+}
+
+template <typename T>
+int launch_rope_vec(const RopeParams& p, cudaStream_t stream) {
+  const int threads = 256, wpc = threads / 32;
+  const int64_t groups = (p.total_rows + 3) / 4;
+  int64_t blocks = (groups + wpc - 1) / wpc;
+  const int64_t cap = 148LL * 16;
+  if (blocks > cap) blocks = cap;
+  cudaError_t e = launch_pdl(qk_rope_store_vec_kernel<T>, dim3((unsigned)blocks), dim3(threads), 0, stream, p);
+  if (e != cudaSuccess) return fail(MVB200_ECUDA, "qk_norm_rope_store: %s", cudaGetErrorString(e));
+  return check_launch("qk_norm_rope_store");
+}
+
 template <typename T>
 int launch_rope(const RopeParams& p, cudaStream_t stream) {
   const int threads = 256, wpc = threads / 32;
@@ -228,6 +374,12 @@ extern "C" int mvb200_qk_norm_rope_store(
                (int64_t)num_tokens * (num_heads + 2 * num_kv_heads), num_heads, num_kv_heads, head_dim};
   note_kernel("qk_norm_rope_store");
   cudaStream_t s = (cudaStream_t)stream;
+  // 128-bit path: 16-bit elements, head_dim 128, every row start 16-byte aligned
+  bool vec_ok = eb == 2 && head_dim == 128 && getenv("MVB200_ROPE_PAIR") == nullptr;
+  for (int64_t st : strides) vec_ok = vec_ok && (st % 8 == 0);
+  for (const void* ptr : ptrs) vec_ok = vec_ok && (reinterpret_cast<uintptr_t>(ptr) % 16 == 0);
+  vec_ok = vec_ok && ((reinterpret_cast<uintptr_t>(cos_cache) | reinterpret_cast<uintptr_t>(sin_cache)) % 16 == 0);
+  if (vec_ok) return dtype == MVB200_F16 ? launch_rope_vec<__half>(p, s) : launch_rope_vec<__nv_bfloat16>(p, s);
   if (dtype == MVB200_F32) return launch_rope<float>(p, s);
   if (dtype == MVB200_F16) return launch_rope<__half>(p, s);
   return launch_rope<__nv_bfloat16>(p, s);
