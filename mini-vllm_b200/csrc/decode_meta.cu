@@ -15,6 +15,8 @@
 // (minivllm/sampling/sampler.py:104-106, GreedySampler :118-130): argmax over the vocabulary, ties to
 // the lowest index, NaN counts as the maximum (torch.argmax semantics).  HBM-bound row reduction:
 // one CTA per (row, vocabulary chunk) with 16-byte loads, a second tiny pass when chunks > 1.
+#include <math.h>
+
 #include "common.cuh"
 
 namespace mvb200 {
@@ -140,23 +142,52 @@ greedy_argmax_kernel(const T* __restrict__ logits, int64_t row_stride, int32_t v
   const T* base = logits + (int64_t)row * row_stride;
   const int32_t lo = blockIdx.x * chunk_elems;
   const int32_t hi = min(vocab, lo + chunk_elems);
-  unsigned long long best = 0ull;
+  // Per thread: running (value, index) with a strict '>' — indices are visited in increasing order, so the
+  // first maximum wins — plus the lowest NaN index; ~6 ALU ops per element instead of a 64-bit key per
+  // element (the kernel was ALU-bound at 1.7 TB/s).  Keys are built once per thread for the reductions.
+  constexpr uint32_t kNone = 0xFFFFFFFFu;
+  float best_v = -INFINITY;
+  uint32_t best_i = kNone, nan_i = kNone, first_i = kNone;
+  auto visit = [&](float v, uint32_t idx) {
+    const bool gt = v > best_v;  // false for NaN
+    best_v = gt ? v : best_v;
+    best_i = gt ? idx : best_i;
+    nan_i = (v != v) ? min(nan_i, idx) : nan_i;
+  };
   const bool aligned = ((reinterpret_cast<uintptr_t>(base) & 15) == 0) && (lo % N == 0);
   int32_t vec_end = lo;
   if (aligned) {
     const int32_t nvec = (hi - lo) / N;
     vec_end = lo + nvec * N;
+    if ((int32_t)threadIdx.x < nvec) first_i = (uint32_t)(lo + threadIdx.x * N);
     const uint4* p = reinterpret_cast<const uint4*>(base + lo);
-    for (int32_t i = threadIdx.x; i < nvec; i += kArgmaxThreads) {
-      const uint4 r = __ldg(p + i);
-      float f[N];
-      Vec16<T>::unpack(r, f);
+    constexpr int U = 4;  // 64 bytes in flight per thread
+    for (int32_t i0 = threadIdx.x; i0 < nvec; i0 += U * kArgmaxThreads) {
+      uint4 r[U];
 #pragma unroll
-      for (int j = 0; j < N; ++j) best = umax64(best, argmax_key(f[j], (uint32_t)(lo + i * N + j)));
+      for (int u = 0; u < U; ++u) {
+        const int32_t i = i0 + u * kArgmaxThreads;
+        r[u] = i < nvec ? __ldg(p + i) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int32_t i = i0 + u * kArgmaxThreads;
+        if (i < nvec) {
+          float f[N];
+          Vec16<T>::unpack(r[u], f);
+#pragma unroll
+          for (int j = 0; j < N; ++j) visit(f[j], (uint32_t)(lo + i * N + j));
+        }
+      }
     }
   }
-  for (int32_t i = vec_end + threadIdx.x; i < hi; i += kArgmaxThreads)
-    best = umax64(best, argmax_key(to_f32(base[i]), (uint32_t)i));
+  if (first_i == kNone && vec_end + (int32_t)threadIdx.x < hi) first_i = (uint32_t)(vec_end + threadIdx.x);
+  for (int32_t i = vec_end + threadIdx.x; i < hi; i += kArgmaxThreads) visit(to_f32(base[i]), (uint32_t)i);
+  // thread result -> key: a NaN beats everything; a thread that saw only -inf offers its first element
+  unsigned long long best = 0ull;
+  if (nan_i != kNone) best = argmax_key(__uint_as_float(0x7FC00000u), nan_i);
+  else if (best_i != kNone) best = argmax_key(best_v, best_i);
+  else if (first_i != kNone) best = argmax_key(-INFINITY, first_i);
   best = block_max_key(best);
   if (threadIdx.x == 0) {
     if (gridDim.x == 1) {

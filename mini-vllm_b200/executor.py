@@ -103,6 +103,10 @@ class HotPathExecutor:
         self.graph_vars: dict[str, torch.Tensor] = {}
         self.graph_splits: dict[int, int] = {}
         self.graph_pool = None
+        # device-resident decode loop (capture_graphs(token_fn=...), begin_decode, step_decode)
+        self._token_fn: Callable[[torch.Tensor, torch.Tensor], None] | None = None
+        self._loop_b = self._loop_bs = 0
+        self._h_app: torch.Tensor | None = None
 
     # ------------------------------------------------------------------ helpers
     def _host(self, shape, dtype) -> torch.Tensor:
@@ -318,7 +322,7 @@ class HotPathExecutor:
         — the state ``decode_advance`` turns into exactly what ``_prepare_decode_input`` (:551-617)
         would build for this step.  Rows beyond ``len(seqs)`` of the bucket become padding.  Returns the
         graph bucket.  Call again whenever the set (or order) of running sequences changes."""
-        if not self.graph_vars or getattr(self, "_token_fn", None) is None:
+        if not self.graph_vars or self._token_fn is None:
             raise RuntimeError("begin_decode needs capture_graphs(token_fn=...)")
         b = len(seqs)
         bs = next((x for x in self.graph_bs if x >= b), None)
@@ -352,6 +356,8 @@ class HotPathExecutor:
         Returns the device vector of the ``b`` tokens picked by ``token_fn``; hidden states of the step
         are in ``graph_vars['outputs'][:b]``."""
         b, bs = self._loop_b, self._loop_bs
+        if bs == 0:
+            raise RuntimeError("step_decode called before begin_decode")
         gv = self.graph_vars
         if appends:
             self._h_app.fill_(-1)
@@ -383,7 +389,7 @@ class HotPathExecutor:
         width = ctx.block_tables.size(1)
         gv["block_tables"][:b, :width] = ctx.block_tables  # stale columns persist beyond `width` (:766-768)
         gv["context_lens"].zero_()
-        if getattr(self, "_token_fn", None) is not None:
+        if self._token_fn is not None:
             # self-advancing graph: hand it the state *before* this step; its first node rebuilds
             # ids/positions/slots/context_lens from it (identical to what prepare_decode staged)
             gv["next_tokens"][:b] = input_ids

@@ -178,6 +178,11 @@ def test_greedy_argmax_matches_oracle(m, cuda_device, dtype, rows, vocab):
         if rows > 2:
             x[2] = 0.0
             x[2, 9] = -0.0
+        if rows > 3:
+            x[3] = -float("inf")          # everything -inf -> index 0
+        if rows > 4:
+            x[4] = -float("inf")
+            x[4, vocab - 2] = -1e30
     want = O.greedy(x.float().numpy())
     val = torch.empty(rows, dtype=torch.float32, device=cuda_device)
     got = m.ops.greedy_argmax(x.to(cuda_device), out_value=val, index_offset=1000)
