@@ -36,7 +36,7 @@ extern "C" {
 #define MVB200_API
 #endif
 
-#define MVB200_VERSION 100
+#define MVB200_VERSION 110
 
 /* element types */
 #define MVB200_F32 0

@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol(native):
     for sym in _declared_symbols():
         assert hasattr(handle, sym), f"{sym} declared in mvb200.h but not exported"
     assert sorted(native.SIGNATURES) == _declared_symbols()
-    assert native.lib().mvb200_version() == 100
+    assert native.lib().mvb200_version() == 110
 
 
 def test_host_side_helpers_need_no_gpu(native):
@@ -81,3 +81,32 @@ def test_ops_refuse_cpu_tensors(native):
     with pytest.raises(ValueError, match="empty"):
         m.paged_decode_attention(z, torch.tensor([]), torch.tensor([]),
                                  torch.zeros(1, 1, dtype=torch.int32), torch.ones(1, dtype=torch.int32), 1.0)
+
+
+def test_custom_torch_ops_are_registered():
+    """the operators are also exposed as torch.ops.mvb200.* with mutation annotated."""
+    import torch
+
+    import minivllm_b200 as m
+
+    for name in m.torch_ops.REGISTERED:
+        assert hasattr(torch.ops.mvb200, name), name
+    schema = str(torch.ops.mvb200.store_kvcache.default._schema)
+    assert "Tensor(a2!) k_cache" in schema and "Tensor(a3!) v_cache" in schema, schema
+    # fake (shape-only) kernels run without a GPU
+    from torch._subclasses.fake_tensor import FakeTensorMode
+
+    with FakeTensorMode():
+        q = torch.empty(3, 16, 128, dtype=torch.bfloat16)
+        kc = torch.empty(8, 64, 8, 128, dtype=torch.bfloat16)
+        bt = torch.empty(3, 4, dtype=torch.int32)
+        cl = torch.empty(3, dtype=torch.int32)
+        out = torch.ops.mvb200.paged_decode(q, kc, kc, bt, cl, 0.1)
+        assert out.shape == q.shape and out.dtype == q.dtype
+        tok = torch.ops.mvb200.greedy_argmax(torch.empty(3, 100, dtype=torch.bfloat16))
+        assert tok.shape == (3,) and tok.dtype == torch.int64
+    # real tensors on CPU: the op refuses, there is no fallback
+    import pytest
+
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        torch.ops.mvb200.greedy_argmax(torch.zeros(2, 10))

@@ -136,6 +136,26 @@ def test_decode_golden(m, cuda_device, case):
     assert np.abs(_f32(out) - o).max() <= TOL[dt]
 
 
+def test_torch_ops_namespace_runs_the_same_kernels(m, cuda_device):
+    """torch.ops.mvb200.* (custom torch ops) == the direct wrappers, bit for bit."""
+    g = load_golden("decode")
+    case = _cases("decode")[0]
+    dt, q, kc, vc, bt, ctx, scale = _decode_inputs(g, case, cuda_device)
+    want = m.paged_decode_attention(q, kc, vc, bt, ctx, scale)
+    got = torch.ops.mvb200.paged_decode(q, kc, vc, bt, ctx, scale)
+    assert torch.equal(got, want)
+    n, kvh, d = 5, kc.size(2), kc.size(3)
+    key = torch.randn(n, kvh, d, device=cuda_device).to(kc.dtype)
+    val = torch.randn(n, kvh, d, device=cuda_device).to(kc.dtype)
+    slots = torch.tensor([3, -1, 0, 7, 1], dtype=torch.int32, device=cuda_device)
+    k1, v1, k2, v2 = kc.clone(), vc.clone(), kc.clone(), vc.clone()
+    m.store_kvcache(key, val, k1, v1, slots)
+    torch.ops.mvb200.store_kvcache(key, val, k2, v2, slots)
+    assert torch.equal(k1, k2) and torch.equal(v1, v2) and not torch.equal(k1, kc)
+    logits = torch.randn(4, 1000, device=cuda_device)
+    assert torch.equal(torch.ops.mvb200.greedy_argmax(logits), logits.argmax(dim=-1))
+
+
 @pytest.mark.parametrize("case", ["qwen3_g2", "qwen3_g4", "qwen2_g7", "qwen2_g8", "opt_mha"])
 @pytest.mark.parametrize("splits", [1, 2, 3, 9])
 def test_decode_split_kv_invariance(m, cuda_device, case, splits):
