@@ -101,9 +101,13 @@ class Attention(nn.Module):
         slots = context.slot_mapping if has_cache and fusable else None
         q, k = ops.qk_norm_rope_store(q, k, v, positions, cos_cache, sin_cache, q_norm_weight, k_norm_weight,
                                       eps, slots, k_cache if has_cache else None, v_cache if has_cache else None)
-        return self.forward(q, k, v, _stored=fusable)
+        return self._attend(q, k, v, stored=fusable)
 
-    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, _stored: bool = False) -> torch.Tensor:
+    def forward(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> torch.Tensor:
+        # exactly the reference's signature (attention.py:196-198)
+        return self._attend(q, k, v, stored=False)
+
+    def _attend(self, q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, *, stored: bool) -> torch.Tensor:
         context = _get_context()
         k_cache, v_cache = self.k_cache, self.v_cache
         has_cache = k_cache.numel() > 0 and v_cache.numel() > 0
@@ -114,7 +118,7 @@ class Attention(nn.Module):
         if has_cache:
             self._cache_initialized = True
             slots = context.slot_mapping
-            if not _stored and slots is not None and slots.numel() > 0:  # attention.py:237-243
+            if not stored and slots is not None and slots.numel() > 0:  # attention.py:237-243
                 ops.store_kvcache(k, v, k_cache, v_cache, slots)
         elif not context.is_prefill and not self._cache_initialized:
             raise RuntimeError(
