@@ -100,6 +100,12 @@ CHILD = textwrap.dedent(
     ref_params = params(set_context)
     assert params(new_context.set_context)[:len(ref_params)] == ref_params
     assert all(d is None for _, d in params(new_context.set_context)[len(ref_params):])
+    import dataclasses
+    from minivllm.utils.context import Context as RefContext
+    ref_fields = [(f.name, f.default) for f in dataclasses.fields(RefContext)]
+    new_fields = [(f.name, f.default) for f in dataclasses.fields(new_context.Context)]
+    assert new_fields[:len(ref_fields)] == ref_fields, (new_fields, ref_fields)
+    assert all(d is None for _, d in new_fields[len(ref_fields):])
     set_context(True, max_seqlen_q=3, max_seqlen_k=3,
                 cum_seqlens_q=torch.tensor([0, 3], dtype=torch.int32),
                 cum_seqlens_k=torch.tensor([0, 3], dtype=torch.int32),
