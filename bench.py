@@ -59,6 +59,57 @@ def kv_bytes_per_layer(batch, ctx, kvh, d, elem=2):
 # ---------------------------------------------------------------------------
 
 
+class HostPipeline:
+    """The e2e leg's per-layer loop over HOST buffers: while layer ``l`` computes on the current stream, layer
+    ``l+1``'s pinned-host q/k/v are copied in on a second stream (two device buffer sets) and layer ``l``'s
+    result goes back to pinned host memory on a third.  Every copy of every step is issued, and finished,
+    inside the timed region (the side streams are fenced against the current stream at both ends of a step);
+    ``MVB200_E2E_SERIAL=1`` puts everything back on one stream for an A/B."""
+
+    def __init__(self, torch, like):
+        self.torch = torch
+        self.serial = os.environ.get("MVB200_E2E_SERIAL", "0") == "1"
+        self.h2d, self.d2h = torch.cuda.Stream(), torch.cuda.Stream()
+        self.bufs = [tuple(torch.empty_like(t) for t in like) for _ in range(2)]
+        self.ready = [torch.cuda.Event() for _ in range(2)]
+        self.consumed = [torch.cuda.Event() for _ in range(2)]
+
+    def _copy_in(self, l, host_in):
+        i = l & 1
+        with self.torch.cuda.stream(self.h2d):
+            if l >= 2:
+                self.h2d.wait_event(self.consumed[i])  # layer l-2 has read this buffer set
+            for dst, src in zip(self.bufs[i], host_in(l)):
+                dst.copy_(src, non_blocking=True)
+            self.ready[i].record(self.h2d)
+
+    def run(self, layers, host_in, host_out):
+        torch = self.torch
+        cur = torch.cuda.current_stream()
+        if self.serial:
+            for l, a in enumerate(layers):
+                for dst, src in zip(self.bufs[0], host_in(l)):
+                    dst.copy_(src, non_blocking=True)
+                host_out(l).copy_(a(*self.bufs[0]), non_blocking=True)
+            return
+        self.h2d.wait_stream(cur)  # nothing of this step starts before the step (and its start event) does
+        self.d2h.wait_stream(cur)
+        self._copy_in(0, host_in)
+        for l, a in enumerate(layers):
+            i = l & 1
+            if l + 1 < len(layers):
+                self._copy_in(l + 1, host_in)
+            cur.wait_event(self.ready[i])
+            o = a(*self.bufs[i])
+            self.consumed[i].record(cur)
+            with torch.cuda.stream(self.d2h):
+                self.d2h.wait_event(self.consumed[i])
+                host_out(l).copy_(o, non_blocking=True)
+            o.record_stream(self.d2h)
+        cur.wait_stream(self.h2d)  # the step ends (and its end event fires) after the last copy out
+        cur.wait_stream(self.d2h)
+
+
 class ClockSampler:
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -307,7 +358,7 @@ def run_b200(args, wl):
     hout = [torch.empty(B, H, D, dtype=torch.bfloat16).pin_memory() for _ in range(L)]
     h_slots, h_ctx, h_bt = slot_mapping.cpu().pin_memory(), context_lens.cpu().pin_memory(), block_tables.cpu().pin_memory()
     d_slots, d_ctx, d_bt = torch.empty_like(slot_mapping), torch.empty_like(context_lens), torch.empty_like(block_tables)
-    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    pipe = HostPipeline(torch, (q, k, v))
 
     def e2e_step():
         d_slots.copy_(h_slots, non_blocking=True)
@@ -315,11 +366,7 @@ def run_b200(args, wl):
         d_bt.copy_(h_bt, non_blocking=True)
         m.set_context(False, slot_mapping=d_slots, context_lens=d_ctx, block_tables=d_bt,
                       decode_num_splits=splits, decode_workspace=workspace if splits > 1 else None)
-        for l, a in enumerate(layers):
-            dq.copy_(hq[l], non_blocking=True)
-            dk.copy_(hk[l], non_blocking=True)
-            dv.copy_(hv[l], non_blocking=True)
-            hout[l].copy_(a(dq, dk, dv), non_blocking=True)
+        pipe.run(layers, lambda l: (hq[l], hk[l], hv[l]), lambda l: hout[l])
 
     ms_e2e = timed(e2e_step, args.steps, args.warmup)
     m.reset_context()
@@ -366,7 +413,7 @@ def run_b200(args, wl):
         },
         "e2e": {"value": bytes_step_job / (ms_e2e * 1e-3) / 1e9, "unit": "GB/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "api": "minivllm_b200.Attention.forward per layer, pinned host q/k/v in, pinned host out"},
+                "api": "minivllm_b200.Attention.forward per layer, pinned host q/k/v in, pinned host out; copies of layer l+1 / l-1 on side streams overlap layer l (serial: MVB200_E2E_SERIAL=1)"},
         "gpu_launches": launches_per_step * args.steps,
         "clocks": clocks.summary(),
     }
@@ -517,17 +564,13 @@ def run_prefill_b200(args, wl):
     hout = torch.empty(N, H, D, dtype=torch.bfloat16).pin_memory()
     h_meta = [t.cpu().pin_memory() for t in (slot_mapping, block_tables, cu_q, cu_k)]
     d_meta = [torch.empty_like(t) for t in (slot_mapping, block_tables, cu_q, cu_k)]
-    dq, dk, dv = torch.empty_like(q), torch.empty_like(k), torch.empty_like(v)
+    pipe = HostPipeline(torch, (q, k, v))
 
     def e2e_step():
         for dst, src in zip(d_meta, h_meta):
             dst.copy_(src, non_blocking=True)
         set_ctx(*d_meta)
-        for a in layers:
-            dq.copy_(hq, non_blocking=True)
-            dk.copy_(hk, non_blocking=True)
-            dv.copy_(hv, non_blocking=True)
-            hout.copy_(a(dq, dk, dv), non_blocking=True)
+        pipe.run(layers, lambda l: (hq, hk, hv), lambda l: hout)
 
     ms_e2e = timed(e2e_step, args.steps, args.warmup)
     m.reset_context()
@@ -560,7 +603,7 @@ def run_prefill_b200(args, wl):
         "e2e": {"value": fl_job / (ms_e2e * 1e-3) / 1e12, "unit": "TFLOP/s", "ms_per_step": ms_e2e,
                 "h2d_bytes_per_step": L * (hq.numel() + hk.numel() + hv.numel()) * 2 + sum(t.numel() for t in h_meta) * 4,
                 "d2h_bytes_per_step": L * hout.numel() * 2,
-                "api": "minivllm_b200.Attention.forward per layer, pinned host q/k/v in, pinned host out"},
+                "api": "minivllm_b200.Attention.forward per layer, pinned host q/k/v in, pinned host out; copies of layer l+1 / l-1 on side streams overlap layer l (serial: MVB200_E2E_SERIAL=1)"},
         "gpu_launches": L * 2 * args.steps,
         "clocks": clocks.summary(),
     }
