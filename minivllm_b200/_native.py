@@ -1,6 +1,6 @@
 """ctypes binding of libmvb200.so (the C ABI declared in include/mvb200.h).
 
-The library is built in-tree by ``mini-vllm_b200/build.py`` (``__graft_entry__.build()``).
+The library is built in-tree by ``minivllm_b200/build.py`` (``__graft_entry__.build()``).
 There is no fallback: if the library is missing or a launcher reports an error the
 caller gets an exception.
 """

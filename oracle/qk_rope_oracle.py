@@ -1,7 +1,7 @@
 """CPU oracle (numpy) for the caller-side sequence in front of the attention hot path.
 
 TEST INFRASTRUCTURE ONLY: imported by ``tests/``, ``__graft_entry__.smoke()`` and the CPU-baseline
-legs of ``bench.py``; never by the product path (``mini-vllm_b200/``).
+legs of ``bench.py``; never by the product path (``minivllm_b200/``).
 
 Restates what ``QwenAttention.forward`` does between the fused qkv GEMM and ``self.attn(q, k, v)``
 (reference ``minivllm/models/qwen_base.py:175-186``) plus the store ``Attention.forward`` starts with

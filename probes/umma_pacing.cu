@@ -17,7 +17,7 @@
 #include <cstdlib>
 #include <vector>
 
-#include "../mini-vllm_b200/csrc/tcgen05.cuh"
+#include "../minivllm_b200/csrc/tcgen05.cuh"
 
 using namespace mvb200;
 

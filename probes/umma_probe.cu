@@ -11,7 +11,7 @@
 #include <cstring>
 #include <vector>
 
-#include "../mini-vllm_b200/csrc/tcgen05.cuh"
+#include "../minivllm_b200/csrc/tcgen05.cuh"
 
 using namespace mvb200;
 

@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Run under torchrun on N GPUs of one node: parity and latency of the fused peer all-reduce + add + RMSNorm
-(mini-vllm_b200/comm.py) against NCCL all_reduce followed by the harness add_rms_norm kernel.
+(minivllm_b200/comm.py) against NCCL all_reduce followed by the harness add_rms_norm kernel.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tests/mp_peer_allreduce_check.py
 

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Per-tile pipeline timeline of the tcgen05 prefill kernel (debug tool, B200 only).
 
-    python mini-vllm_b200/build.py --trace        # here: builds libmvb200_trace.so (-DPF_TRACE)
+    python minivllm_b200/build.py --trace        # here: builds libmvb200_trace.so (-DPF_TRACE)
     python tools/prefill_trace.py                  # on the GPU box
 
 One CTA (longest query tile of a middle head/sequence) records clock64 at every hand-off of its TMA
@@ -13,7 +13,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-os.environ["MVB200_LIB"] = os.path.join(ROOT, "mini-vllm_b200", "libmvb200_trace.so")
+os.environ["MVB200_LIB"] = os.path.join(ROOT, "minivllm_b200", "libmvb200_trace.so")
 V1 = "--v1" in sys.argv  # trace the one-query-tile kernel instead of the persistent two-tile one
 if V1:
     os.environ["MVB200_PREFILL_V1"] = "1"
