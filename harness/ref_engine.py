@@ -1,0 +1,193 @@
+"""Run the reference's own engine (``minivllm.LLM.generate``) — optionally with the B200 layer swapped in.
+
+This is the drop-in boundary exercised for real: the reference's
+``LLM`` / ``LLMEngine`` / ``Scheduler`` / ``BlockManager`` / ``ModelRunner`` /
+``InferenceExecutor`` / model definitions / sampler all run unmodified (imported from
+``/root/reference`` or its copy under ``oracle/_ref``); ``minivllm_b200.install_into_reference()``
+replaces the ``Attention`` layer (and, with ``executor=True``, the executor's metadata
+preparation / cache sizing / CUDA-Graph capture, the three subsystems north_star says change).
+
+Arms:
+  device=cpu                      the reference's eager path on the host cores (the oracle / CPU baseline)
+  device=cuda, dropin=True        reference engine + sm_100a kernels (the product as a user would run it)
+  device=cuda, dropin=False       the reference's own CUDA path (flash-attn / Triton) if the wheels run on sm_100
+
+Harness code: imports ``oracle.reference_engine`` for the loader/tokenizer/config patches.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def make_prompts(vocab: int, lens: list[int], seed: int = 600) -> list[list[int]]:
+    import torch
+
+    g = torch.Generator().manual_seed(seed)
+    return [torch.randint(10, vocab - 10, (n,), generator=g).tolist() for n in lens]
+
+
+def run(
+    preset: str,
+    *,
+    device: str = "cpu",
+    dtype: str = "float32",
+    dropin: bool = False,
+    executor: bool = False,
+    calls: list[list[list[int]]],
+    max_tokens: int = 32,
+    enforce_eager: bool = True,
+    fast_init: bool = False,
+    record_logits: bool = False,
+    hide_flash_attn: bool | None = None,
+    threads: int | None = None,
+    config_overrides: dict | None = None,
+    **config_kw,
+) -> dict:
+    """Build one reference ``LLM`` and run ``generate`` once per entry of ``calls`` (later calls can hit the
+    prefix cache of earlier ones, block_manager.py:252-339).  Returns tokens, per-step timings and counters."""
+    from oracle import reference_engine as R
+
+    if hide_flash_attn is None:
+        hide_flash_attn = device == "cpu" or dropin
+    R.import_reference(device, hide_flash_attn=hide_flash_attn)
+    import torch
+
+    if threads:
+        torch.set_num_threads(threads)
+    info: dict = {"preset": preset, "device": device, "dtype": dtype, "dropin": dropin, "executor": executor,
+                  "enforce_eager": enforce_eager, "reference_root": R.locate_reference()}
+    if dropin:
+        import minivllm_b200
+
+        minivllm_b200.install_into_reference(executor=executor)
+        info["native_lib"] = minivllm_b200._native.LIB_PATH
+    elif executor:  # executor subsystems only, the reference's own attention layer (CPU-testable)
+        from minivllm_b200 import reference_patch
+
+        reference_patch.install_executor()
+    loader = R.fast_device_load("cuda:0" if device == "cuda" else "cpu", dtype) if fast_init else R.seeded_load
+    t0 = time.perf_counter()
+    llm = R.make_llm(preset, dtype=dtype, loader=loader, enforce_eager=enforce_eager,
+                     config_overrides=config_overrides, **config_kw)
+    info["init_s"] = time.perf_counter() - t0
+    attn_cls = {type(m).__module__ + "." + type(m).__name__ for m in llm.model_runner.model_manager.model.modules()
+                if hasattr(m, "k_cache")}
+    info["attention_classes"] = sorted(attn_cls)
+    sync = (lambda: torch.cuda.synchronize()) if device == "cuda" else (lambda: None)
+
+    steps: list[tuple[int, float]] = []
+    inner_step = llm.step
+
+    def timed_step():
+        sync()
+        t = time.perf_counter()
+        out = inner_step()
+        sync()
+        steps.append((out[1], time.perf_counter() - t))
+        return out
+
+    llm.step = timed_step
+    # top-2 logits of every sampled row, in batch order (stronger than token ids: a near-tie is visible)
+    top_log: list = []
+    if record_logits:
+        ex0 = llm.model_runner.inference_executor
+        inner_sample = ex0._sample_tokens
+
+        def sampling(logits, sequences):
+            v, i = logits.float().topk(2, dim=-1)
+            top_log.append(([s.seq_id for s in sequences], v.cpu().tolist(), i.cpu().tolist()))
+            return inner_sample(logits, sequences)
+
+        ex0._sample_tokens = sampling
+    sp = R.greedy_params(max_tokens)
+    results = []
+    for prompts in calls:
+        steps.clear()
+        top_log.clear()
+        hits0 = llm.scheduler.block_manager.stats.get("cache_hits", 0)
+        t0 = time.perf_counter()
+        res = llm.generate(prompts, sp, use_tqdm=False)
+        sync()
+        wall = time.perf_counter() - t0
+        pre = [(n, t) for n, t in steps if n > 0]
+        dec = [(-n, t) for n, t in steps if n < 0]
+        results.append({
+            "tokens": [r["token_ids"] for r in res],
+            "wall_s": wall,
+            "cache_hits": llm.scheduler.block_manager.stats.get("cache_hits", 0) - hits0,
+            "prefill_tokens": sum(n for n, _ in pre), "prefill_s": sum(t for _, t in pre),
+            "decode_tokens": sum(n for n, _ in dec), "decode_s": sum(t for _, t in dec),
+            "decode_steps": len(dec),
+        })
+        if record_logits:
+            # regroup per sequence in request order: top2[p][t] = (v1, v2, id1, id2)
+            ids = sorted({sid for sids, _, _ in top_log for sid in sids})
+            per = {sid: [] for sid in ids}
+            for sids, vals, idx in top_log:
+                for sid, v, i in zip(sids, vals, idx):
+                    per[sid].append((v[0], v[1], i[0], i[1]))
+            results[-1]["top2"] = [per[sid] for sid in ids]
+    info["calls"] = results
+    if dropin:
+        import minivllm_b200
+
+        info["last_kernel"] = minivllm_b200.ops.last_kernel()
+        info["kernels_seen"] = sorted(minivllm_b200.ops.kernels_seen())
+    ex = llm.model_runner.inference_executor
+    info["graphs_captured"] = sorted(getattr(ex, "graphs", {}).keys())
+    try:
+        llm.exit()
+    except Exception as e:  # the reference's cleanup is best-effort
+        info["exit_error"] = repr(e)
+    return info
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--preset", default="qwen3-0.6b")
+    ap.add_argument("--device", default="cpu")
+    ap.add_argument("--dtype", default="float32")
+    ap.add_argument("--dropin", action="store_true")
+    ap.add_argument("--executor", action="store_true")
+    ap.add_argument("--graphs", action="store_true")
+    ap.add_argument("--fast-init", action="store_true")
+    ap.add_argument("--lens", default="165,13,203,64,250")
+    ap.add_argument("--repeat-call", type=int, default=1, help="issue the same prompts this many times (2nd+ hit the prefix cache)")
+    ap.add_argument("--max-tokens", type=int, default=32)
+    ap.add_argument("--max-num-seqs", type=int, default=8)
+    ap.add_argument("--max-model-len", type=int, default=1024)
+    ap.add_argument("--max-num-batched-tokens", type=int, default=16384)
+    ap.add_argument("--num-kvcache-blocks", type=int, default=64)
+    ap.add_argument("--threads", type=int, default=0)
+    ap.add_argument("--golden", default="", help="npz with <preset>.<dtype>.prompt{i}/tokens{i}: compare instead of free-running")
+    ap.add_argument("--out", default="")
+    a = ap.parse_args()
+    from oracle import reference_engine as R
+
+    vocab = R.PRESETS[a.preset]["vocab_size"]
+    prompts = make_prompts(vocab, [int(x) for x in a.lens.split(",")])
+    info = run(a.preset, device=a.device, dtype=a.dtype, dropin=a.dropin, executor=a.executor,
+               calls=[prompts] * a.repeat_call, max_tokens=a.max_tokens, enforce_eager=not a.graphs,
+               fast_init=a.fast_init, threads=a.threads or None, max_num_seqs=a.max_num_seqs,
+               max_model_len=a.max_model_len, max_num_batched_tokens=a.max_num_batched_tokens,
+               num_kvcache_blocks=a.num_kvcache_blocks)
+    slim = {k: v for k, v in info.items() if k != "calls"}
+    slim["calls"] = [{k: v for k, v in c.items() if k != "tokens"} | {"first_tokens": [t[:6] for t in c["tokens"]]}
+                     for c in info["calls"]]
+    print(json.dumps(slim))
+    if a.out:
+        with open(a.out, "w") as f:
+            json.dump(info, f)
+
+
+if __name__ == "__main__":
+    main()

@@ -56,6 +56,11 @@ MVB200_API const char* mvb200_last_error(void);
  * ("decode_tma_mma", "decode_generic", "prefill_tcgen05", "prefill_generic", "store_vec16", ...). */
 MVB200_API const char* mvb200_last_kernel(void);
 
+/* Comma-separated list of the distinct kernel families this process has dispatched to so far, written
+ * to buf (NUL-terminated, truncated to cap); returns their count.  Diagnostic: lets a host engine that
+ * swapped the layer in prove which kernels its run actually launched. */
+MVB200_API int mvb200_kernels_seen(char* buf, int cap);
+
 /*
  * store_kvcache — scatter new K/V rows into the paged cache.
  * Replaces StandardAttentionBackend.store_kv_cache (models/layers/attention_backend.py:196-266)

@@ -22,6 +22,7 @@ SIGNATURES = {
     "mvb200_version": (c_int32, []),
     "mvb200_last_error": (c_char_p, []),
     "mvb200_last_kernel": (c_char_p, []),
+    "mvb200_kernels_seen": (c_int32, [c_char_p, c_int32]),
     "mvb200_store_kvcache": (
         c_int32,
         [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p,
@@ -109,6 +110,12 @@ def last_error() -> str:
 
 def last_kernel() -> str:
     return (lib().mvb200_last_kernel() or b"").decode()
+
+
+def kernels_seen() -> list[str]:
+    buf = ctypes.create_string_buffer(2048)
+    lib().mvb200_kernels_seen(buf, len(buf))
+    return [k for k in buf.value.decode().split(",") if k]
 
 
 def check(rc: int, what: str) -> None:

@@ -159,13 +159,18 @@ class Attention(nn.Module):
         )
 
 
-def install_into_reference() -> None:
+def install_into_reference(executor: bool = False) -> None:
     """Swap this layer into an importable ``minivllm`` (the reference) before models are built.
 
     Every reference model imports the class by name from ``minivllm.models.layers``
     (layers/__init__.py:22; qwen_base.py, opt.py, gpt2.py), so the name is rebound
     in each of those modules, and ``forward`` is pointed at the reference's own
     ``get_context`` so that its executor's ``set_context`` calls are seen.
+
+    ``executor=True`` additionally rebinds the attention-metadata preparation, the per-rank cache
+    sizing and the CUDA-Graph capture/replay of the reference's ``InferenceExecutor``
+    (``reference_patch.py``); without it only the layer changes and the engine must run with
+    ``enforce_eager=True`` (the reference's own capture is broken).
     """
     import importlib
 
@@ -185,3 +190,7 @@ def install_into_reference() -> None:
             continue
         if hasattr(mod, "Attention"):
             mod.Attention = Attention
+    if executor:
+        from . import reference_patch
+
+        reference_patch.install_executor()

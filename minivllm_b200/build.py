@@ -17,10 +17,11 @@ SOURCES = [
     "peer_allreduce.cu",
     "paged_decode.cu",
     "prefill_generic.cu",
-    "prefill_tcgen05.cu",
     "prefill_fa2q.cu",
     "prefill_api.cu",
 ]
+# tuning build only (--trace): the first-generation prefill kernel and the knob matrix of the 2q kernel
+TUNING_SOURCES = ["prefill_tcgen05.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
@@ -53,18 +54,19 @@ def build(force: bool = False, verbose: bool = False, trace: bool = False) -> st
     ``trace=True`` builds libmvb200_trace.so from the same sources with -DPF_TRACE (the prefill kernel
     records a per-tile clock64 timeline; used by tools/prefill_trace.py, never by the product path)."""
     if trace:
-        return _build(os.path.join(HERE, "libmvb200_trace.so"), os.path.join(HERE, "build_trace"), ["-DPF_TRACE"], verbose)
+        return _build(os.path.join(HERE, "libmvb200_trace.so"), os.path.join(HERE, "build_trace"),
+                      ["-DPF_TRACE", "-DMVB200_TUNING"], verbose, SOURCES + TUNING_SOURCES)
     if not force and not needs_build():
         return LIB
-    return _build(LIB, os.path.join(HERE, "build"), [], verbose)
+    return _build(LIB, os.path.join(HERE, "build"), [], verbose, SOURCES)
 
 
-def _build(LIB: str, objdir: str, extra: list, verbose: bool) -> str:
+def _build(LIB: str, objdir: str, extra: list, verbose: bool, sources: list) -> str:
     os.makedirs(objdir, exist_ok=True)
     nvcc = _nvcc()
     procs = []
     objs = []
-    for src in SOURCES:
+    for src in sources:
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
         objs.append(obj)
         cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]

@@ -29,6 +29,12 @@ int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, int rank
 // the stream drains; it must execute pdl_wait() before it touches anything a predecessor wrote (or
 // still reads).  Capturable into CUDA graphs.  MVB200_NO_PDL=1 falls back to a plain launch.
 bool pdl_enabled();
+// largest dynamic-smem size a kernel has been opted into, per device (one static instance per kernel)
+struct SmemOptIn {
+  int bytes[64];
+};
+int optin_dynamic_smem(const void* kernel, int bytes, SmemOptIn* cache, const char* what);
+int device_sm_count();  // SMs of the current device (cached per device)
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                               cudaStream_t stream, Args&&... args) {

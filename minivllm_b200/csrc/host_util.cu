@@ -19,11 +19,57 @@ int fail(int code, const char* fmt, ...) {
   return code;
 }
 
-void note_kernel(const char* name) { g_kernel = name; }
+// distinct kernel families launched by this process (names are string literals; a handful at most)
+static const char* g_seen[64];
+static int g_seen_n = 0;
+
+void note_kernel(const char* name) {
+  if (g_kernel == name) return;
+  g_kernel = name;
+  int n = g_seen_n;
+  for (int i = 0; i < n; ++i)
+    if (g_seen[i] == name || strcmp(g_seen[i], name) == 0) return;
+  if (n < 64) {
+    g_seen[n] = name;
+    g_seen_n = n + 1;  // racing threads may drop or duplicate an entry: diagnostic only
+  }
+}
 
 int check_launch(const char* what) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return fail(MVB200_ECUDA, "%s: %s", what, cudaGetErrorString(e));
+  return MVB200_OK;
+}
+
+// Per-device caches: cudaFuncSetAttribute and the SM count are properties of the CURRENT device, and one
+// thread may drive several GPUs (torch.cuda.device switches in a single-process multi-GPU host).
+static constexpr int kMaxDevices = 64;
+
+static int current_device_slot() {
+  int d = 0;
+  if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= kMaxDevices) d = 0;
+  return d;
+}
+
+int device_sm_count() {
+  static int count[kMaxDevices];
+  const int d = current_device_slot();
+  if (count[d] <= 0) {
+    int n = 0;
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, d);
+    count[d] = n > 0 ? n : 148;
+  }
+  return count[d];
+}
+
+int optin_dynamic_smem(const void* kernel, int bytes, SmemOptIn* cache, const char* what) {
+  const int d = current_device_slot();
+  if (cache->bytes[d] >= bytes) return MVB200_OK;
+  cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e != cudaSuccess)
+    return fail(MVB200_ECUDA, "%s: smem opt-in %d B failed on device %d: %s", what, bytes, d,
+                cudaGetErrorString(e));
+  cache->bytes[d] = bytes;
   return MVB200_OK;
 }
 
@@ -88,4 +134,15 @@ extern "C" {
 int mvb200_version(void) { return MVB200_VERSION; }
 const char* mvb200_last_error(void) { return mvb200::g_err; }
 const char* mvb200_last_kernel(void) { return mvb200::g_kernel; }
+int mvb200_kernels_seen(char* buf, int cap) {
+  int used = 0;
+  if (cap > 0) buf[0] = 0;
+  for (int i = 0; i < mvb200::g_seen_n; ++i) {
+    int w = snprintf(buf + used, cap > used ? (size_t)(cap - used) : 0, "%s%s", i ? "," : "",
+                     mvb200::g_seen[i]);
+    if (w < 0 || used + w >= cap) break;
+    used += w;
+  }
+  return mvb200::g_seen_n;
+}
 }

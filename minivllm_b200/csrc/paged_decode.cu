@@ -486,14 +486,9 @@ static int launch_fast(const DecodeParams& p, const void* k_cache, const void* v
   if (smem < merge_bytes) smem = merge_bytes;
   smem += 1024;  // alignment slack
   auto kern = paged_decode_kernel<T, D>;
-  static thread_local int configured = 0;
-  if (configured < smem) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess)
-      return fail(MVB200_ECUDA, "paged_decode: smem opt-in %d B failed: %s", smem,
-                  cudaGetErrorString(e));
-    configured = smem;
-  }
+  static SmemOptIn optin;
+  rc = optin_dynamic_smem((const void*)kern, smem, &optin, "paged_decode");
+  if (rc) return rc;
   dim3 grid(p.num_kv_heads, p.num_splits, batch);
   cudaError_t le = launch_pdl(kern, grid, dim3(kDecodeThreads), (size_t)smem, stream, mk, mv, p);
   if (le != cudaSuccess)

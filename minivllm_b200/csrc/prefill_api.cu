@@ -17,8 +17,12 @@ int prefill_generic_dispatch(const void* q, int64_t q_row_stride, const void* k,
                              cudaStream_t stream);
 
 // return -1 when the request is outside what the kernel covers
-int prefill_tcgen05_dispatch(const PrefillArgs& a, cudaStream_t stream);  // one query tile per CTA
 int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream);     // persistent, two query tiles per CTA
+#ifdef MVB200_TUNING
+// first-generation kernel (one query tile per CTA): A/B tool of the tuning build only
+// (python minivllm_b200/build.py --trace), not part of libmvb200.so
+int prefill_tcgen05_dispatch(const PrefillArgs& a, cudaStream_t stream);
+#endif
 
 }  // namespace mvb200
 
@@ -53,14 +57,21 @@ extern "C" int mvb200_prefill_varlen(
                 block_tables, bt_row_stride, cu_seqlens_q, cu_seqlens_k, out, out_row_stride,
                 num_seqs, total_q, max_seqlen_q, max_seqlen_k, num_heads, num_kv_heads, head_dim,
                 block_size, num_blocks, max_blocks_per_seq, scale, dtype};
-  const bool force_generic = getenv("MVB200_PREFILL_GENERIC") != nullptr;  // debugging aid
-  const bool force_v1 = getenv("MVB200_PREFILL_V1") != nullptr;            // A/B profiling aid
+#ifdef MVB200_TUNING
+  const bool force_generic = getenv("MVB200_PREFILL_GENERIC") != nullptr;
+  const bool force_v1 = getenv("MVB200_PREFILL_V1") != nullptr;
   if (!force_generic) {
     int rc = force_v1 ? -1 : prefill_fa2q_dispatch(a, s);
     if (rc >= 0) return rc;
     rc = prefill_tcgen05_dispatch(a, s);
     if (rc >= 0) return rc;
   }
+#else
+  {
+    const int rc = prefill_fa2q_dispatch(a, s);
+    if (rc >= 0) return rc;
+  }
+#endif
   return prefill_generic_dispatch(q, q_row_stride, k, v, k_row_stride, v_row_stride, k_cache,
                                   v_cache, block_tables, bt_row_stride, cu_seqlens_q, cu_seqlens_k,
                                   out, out_row_stride, num_seqs, total_q, num_heads, num_kv_heads,

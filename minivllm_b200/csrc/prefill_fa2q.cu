@@ -604,18 +604,9 @@ static int launch(const PrefillArgs& a, cudaStream_t stream) {
 
   constexpr int smem = (kQTiles + 2 * kStages) * kTileBytes + 8 * BAR_COUNT + 16 + 1024;
   auto kern = prefill_fa2q_kernel<T, kEmu, kPC>;
-  static thread_local bool configured = false;
-  static thread_local int num_sms = 0;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess)
-      return fail(MVB200_ECUDA, "prefill: smem opt-in %d B failed: %s", smem, cudaGetErrorString(e));
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (num_sms <= 0) num_sms = 148;
-    configured = true;
-  }
+  static SmemOptIn optin;
+  if (int rc = optin_dynamic_smem((const void*)kern, smem, &optin, "prefill_fa2q")) return rc;
+  const int num_sms = device_sm_count();
   const long long items = (long long)p.levels * a.num_seqs * a.num_heads;
   const int grid = (int)(items < num_sms ? items : num_sms);  // persistent: one CTA per SM
   kern<<<grid, kThreads, smem, stream>>>(mq, mk, mv, p);
@@ -641,8 +632,11 @@ int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream) {
       return -1;
   }
   note_kernel("prefill_tcgen05_2q");
-  // Columns (of every 128) whose exponential runs on the FMA pipe instead of MUFU.  Tuning knob for
-  // profiling only (MVB200_PREFILL_EMU = 0 | 16 | 32 | 48, MVB200_PREFILL_PCHUNKS = 1 | 2 | 4); the default is the measured optimum.
+  const bool bf = a.dtype == MVB200_BF16;
+#ifdef MVB200_TUNING
+  // Tuning build only (python minivllm_b200/build.py --trace): columns of every 128 whose exponential
+  // runs on the FMA pipe instead of MUFU (MVB200_PREFILL_EMU = 0 | 16 | 32 | 48) and the P hand-off
+  // granularity (MVB200_PREFILL_PCHUNKS = 1 | 2 | 4).  The product library carries the measured optimum only.
   static const int emu = [] {
     const char* e = getenv("MVB200_PREFILL_EMU");
     const int v = e ? atoi(e) : fa2q::kDefaultEmu;
@@ -653,7 +647,6 @@ int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream) {
     const int v = e ? atoi(e) : fa2q::kDefaultPChunks;
     return (v == 1 || v == 2 || v == 4) ? v : fa2q::kDefaultPChunks;
   }();
-  const bool bf = a.dtype == MVB200_BF16;
 #define MVB_FA2Q_CASE(E, C) \
   if (emu == E && pchunks == C) return bf ? fa2q::launch<__nv_bfloat16, E, C>(a, stream) : fa2q::launch<__half, E, C>(a, stream);
   MVB_FA2Q_CASE(0, 1) MVB_FA2Q_CASE(0, 2) MVB_FA2Q_CASE(0, 4)
@@ -662,6 +655,10 @@ int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream) {
   MVB_FA2Q_CASE(48, 1) MVB_FA2Q_CASE(48, 2) MVB_FA2Q_CASE(48, 4)
 #undef MVB_FA2Q_CASE
   return fail(MVB200_EINVAL, "prefill: no kernel instance for emu %d / pchunks %d", emu, pchunks);
+#else
+  return bf ? fa2q::launch<__nv_bfloat16, fa2q::kDefaultEmu, fa2q::kDefaultPChunks>(a, stream)
+            : fa2q::launch<__half, fa2q::kDefaultEmu, fa2q::kDefaultPChunks>(a, stream);
+#endif
 }
 
 }  // namespace mvb200

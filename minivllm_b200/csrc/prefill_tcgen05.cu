@@ -478,13 +478,8 @@ static int launch(const PrefillArgs& a, cudaStream_t stream) {
 
   constexpr int smem = kQBytes + 2 * kKVStages * kKVBytes + 8 * BAR_COUNT + 16 + 1024;
   auto kern = prefill_tcgen05_kernel<T, kEmu>;
-  static thread_local bool configured = false;
-  if (!configured) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess)
-      return fail(MVB200_ECUDA, "prefill: smem opt-in %d B failed: %s", smem, cudaGetErrorString(e));
-    configured = true;
-  }
+  static SmemOptIn optin;
+  if (int rc = optin_dynamic_smem((const void*)kern, smem, &optin, "prefill_tcgen05")) return rc;
   const int qtiles = (a.max_seqlen_q + kBM - 1) / kBM;
   dim3 grid(qtiles, a.num_heads, a.num_seqs);
   kern<<<grid, kThreads, smem, stream>>>(mq, mk, mv, p);

@@ -480,3 +480,8 @@ def greedy_argmax(
 def last_kernel() -> str:
     """Kernel family the last call on this thread dispatched to (for tests / bench)."""
     return _native.last_kernel()
+
+
+def kernels_seen() -> list[str]:
+    """Distinct kernel families this process has launched so far (``mvb200_kernels_seen``)."""
+    return _native.kernels_seen()

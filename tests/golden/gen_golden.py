@@ -528,6 +528,64 @@ def gen_engine():
 
 
 # ---------------------------------------------------------------------------
+# end to end on the NAMED architectures: the reference's LLM.generate, eager, on CPU
+# ---------------------------------------------------------------------------
+
+ENGINE_NAMED_CASES = [
+    # tag, preset, dtype, prompt lengths, config overrides
+    ("qwen3-0.6b.float32", "qwen3-0.6b", "float32", [165, 13, 203, 64, 250], {}),
+    # same dims with an untied lm_head: with tied random embeddings the argmax is mostly the input token
+    # (the stream is still recorded above, it is the named config); untied, every token depends on the layers
+    ("qwen3-0.6b-untied.float32", "qwen3-0.6b", "float32", [165, 13, 203, 64, 250], {"tie_word_embeddings": False}),
+    ("qwen3-0.6b-untied.bfloat16", "qwen3-0.6b", "bfloat16", [165, 13, 203, 64, 250], {"tie_word_embeddings": False}),
+    # cfg1: examples/cpu_inference_opt.py:143-151 (max_num_seqs=8, max_model_len=1024, eager, float32), OPT-125M dims
+    ("opt-125m.float32", "opt-125m", "float32", [165, 13, 203, 64, 250, 511], {}),
+]
+
+
+def engine_named_prompts(vocab: int, lens):
+    """Call A: distinct prompts.  Call B: two prompts that share 128 / 192 leading tokens with A[0] / A[2]
+    (two / three full blocks) — issued after A on one engine they hit the prefix cache."""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from harness.ref_engine import make_prompts
+
+    a = make_prompts(vocab, lens, seed=600)
+    tails = make_prompts(vocab, [70, 30], seed=601)
+    b = [a[0][:128] + tails[0], a[2][:192] + tails[1]]
+    return a, b
+
+
+def gen_engine_named():
+    """``LLM.generate`` (llm_engine.py:261-367) with ``enforce_eager=True`` on CPU.  Call B is recorded on a
+    FRESH engine (no prefix hit): the reference's eager prefill mis-slices K/V under a hit,
+    and a prompt's greedy stream does not depend on whether its prefix was cached — so the no-hit stream is
+    the truth the GPU run (which does hit) is compared with."""
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from harness import ref_engine
+    from oracle.reference_engine import PRESETS
+
+    out = {}
+    tags = []
+    for tag, preset, dtype, lens, overrides in ENGINE_NAMED_CASES:
+        a, b = engine_named_prompts(PRESETS[preset]["vocab_size"], lens)
+        kw = dict(device="cpu", dtype=dtype, max_tokens=32, record_logits=True, config_overrides=overrides,
+                  max_num_seqs=8, max_model_len=1024, num_kvcache_blocks=64)
+        for call, prompts in (("a", a), ("b", b)):
+            info = ref_engine.run(preset, calls=[prompts], **kw)
+            res = info["calls"][0]
+            assert res["cache_hits"] == 0
+            out[f"{tag}.{call}.n"] = np.array(len(prompts))
+            for i, p in enumerate(prompts):
+                out[f"{tag}.{call}.prompt{i}"] = np.array(p, dtype=np.int64)
+                out[f"{tag}.{call}.tokens{i}"] = np.array(res["tokens"][i], dtype=np.int64)
+                out[f"{tag}.{call}.top2_{i}"] = np.array(res["top2"][i], dtype=np.float64)  # [steps, (v1, v2, id1, id2)]
+            print("   ", tag, call, [t[:6] for t in res["tokens"]])
+        tags.append(tag)
+    out["cases"] = np.array(tags)
+    save("engine_named", **out)
+
+
+# ---------------------------------------------------------------------------
 # caller side (SURVEY 8(f) rank 2): q/k RMSNorm -> RoPE -> store, as QwenAttention.forward does it
 # ---------------------------------------------------------------------------
 
@@ -641,6 +699,8 @@ def gen_arnorm():
 if __name__ == "__main__":
     print("generating golden vectors from", REFERENCE)
     only = set(sys.argv[1:])
-    for fn in (gen_store, gen_decode, gen_prefill, gen_layer, gen_metadata, gen_engine, gen_qkrope, gen_arnorm):
+    for fn in (gen_store, gen_decode, gen_prefill, gen_layer, gen_metadata, gen_engine, gen_engine_named, gen_qkrope, gen_arnorm):
+        if not only and fn is gen_engine_named and os.environ.get('MVB200_SKIP_SLOW_GOLDEN'):
+            continue
         if not only or fn.__name__[4:] in only:
             fn()
