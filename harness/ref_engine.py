@@ -43,13 +43,16 @@ def run(
     dropin: bool = False,
     executor: bool = False,
     calls: list[list[list[int]]],
-    max_tokens: int = 32,
+    max_tokens: int | list[int] = 32,
     enforce_eager: bool = True,
     fast_init: bool = False,
     record_logits: bool = False,
     hide_flash_attn: bool | None = None,
     threads: int | None = None,
     config_overrides: dict | None = None,
+    tensor_parallel_size: int = 1,
+    under_torchrun: bool = False,
+    isolate_cuda: bool = True,
     **config_kw,
 ) -> dict:
     """Build one reference ``LLM`` and run ``generate`` once per entry of ``calls`` (later calls can hit the
@@ -58,7 +61,7 @@ def run(
 
     if hide_flash_attn is None:
         hide_flash_attn = device == "cpu" or dropin
-    R.import_reference(device, hide_flash_attn=hide_flash_attn)
+    R.import_reference(device, hide_flash_attn=hide_flash_attn, isolate_cuda=isolate_cuda)
     import torch
 
     if threads:
@@ -74,10 +77,36 @@ def run(
         from minivllm_b200 import reference_patch
 
         reference_patch.install_executor()
-    loader = R.fast_device_load("cuda:0" if device == "cuda" else "cpu", dtype) if fast_init else R.seeded_load
+    local = int(os.environ.get("LOCAL_RANK", "0")) if under_torchrun else 0
+    rank = int(os.environ.get("RANK", "0")) if under_torchrun else 0
+    loader = R.fast_device_load(f"cuda:{local}" if device == "cuda" else "cpu", dtype, seed=1234 + rank) if fast_init else R.seeded_load
     t0 = time.perf_counter()
-    llm = R.make_llm(preset, dtype=dtype, loader=loader, enforce_eager=enforce_eager,
-                     config_overrides=config_overrides, **config_kw)
+    if tensor_parallel_size > 1:
+        # One process per GPU already exists (torchrun): the reference's LLMEngine must not spawn its own workers
+        # (llm_engine.py:82-100) and its ModelRunner must not tear down a process group it did not create.
+        config_kw["tensor_parallel_size"] = tensor_parallel_size
+        if not under_torchrun:
+            raise ValueError("tensor_parallel_size > 1 is driven from torchrun ranks (under_torchrun=True)")
+        worker = _tp_setup(rank)
+        if worker:
+            from minivllm.config import Config
+            from minivllm.engine.model_runner import ModelRunner
+
+            path = R.write_model_dir(preset, dtype, **(config_overrides or {}))
+            with R.engine_patches(loader):
+                # blocks in ModelRunner._worker_loop (model_runner.py:124-171) until rank 0 broadcasts "exit"
+                ModelRunner(Config(model=path, dtype=dtype, enforce_eager=enforce_eager, **config_kw), rank, _NoSpawn().Event())
+            return {"worker": True, "rank": rank}
+        from unittest import mock
+
+        import minivllm.engine.llm_engine as llm_engine
+
+        with mock.patch.object(llm_engine.mp, "get_context", lambda *_a, **_k: _NoSpawn()):
+            llm = R.make_llm(preset, dtype=dtype, loader=loader, enforce_eager=enforce_eager,
+                             config_overrides=config_overrides, **config_kw)
+    else:
+        llm = R.make_llm(preset, dtype=dtype, loader=loader, enforce_eager=enforce_eager,
+                         config_overrides=config_overrides, **config_kw)
     info["init_s"] = time.perf_counter() - t0
     attn_cls = {type(m).__module__ + "." + type(m).__name__ for m in llm.model_runner.model_manager.model.modules()
                 if hasattr(m, "k_cache")}
@@ -108,9 +137,9 @@ def run(
             return inner_sample(logits, sequences)
 
         ex0._sample_tokens = sampling
-    sp = R.greedy_params(max_tokens)
     results = []
-    for prompts in calls:
+    for ci, prompts in enumerate(calls):
+        sp = R.greedy_params(max_tokens[ci] if isinstance(max_tokens, (list, tuple)) else max_tokens)
         steps.clear()
         top_log.clear()
         hits0 = llm.scheduler.block_manager.stats.get("cache_hits", 0)
@@ -144,11 +173,58 @@ def run(
         info["kernels_seen"] = sorted(minivllm_b200.ops.kernels_seen())
     ex = llm.model_runner.inference_executor
     info["graphs_captured"] = sorted(getattr(ex, "graphs", {}).keys())
+    info["kv_heads_per_rank"] = int(ex.kv_cache.size(4)) if ex.kv_cache is not None else None
     try:
         llm.exit()
     except Exception as e:  # the reference's cleanup is best-effort
         info["exit_error"] = repr(e)
     return info
+
+
+class _NoSpawn:
+    """Stands in for ``mp.get_context("spawn")`` in LLMEngine.__init__ when torchrun already started one
+    process per GPU: no worker is spawned, ``exit()`` finds nothing to join."""
+
+    class _Proc:
+        def start(self):
+            pass
+
+        def join(self, timeout=None):
+            pass
+
+        def is_alive(self):
+            return False
+
+        def terminate(self):
+            pass
+
+        kill = terminate
+
+    def Event(self):
+        import threading
+
+        return threading.Event()
+
+    def Process(self, target=None, args=(), kwargs=None):
+        return self._Proc()
+
+
+def _tp_setup(rank: int) -> bool:
+    """Harness-level fixes that let the reference's TP run inside torchrun ranks.  Returns True on workers."""
+    import torch.distributed as dist
+
+    import minivllm.engine.distributed_manager as dm
+
+    if not dist.is_initialized():
+        raise RuntimeError("under_torchrun: init_process_group first (the model must see the group, SURVEY 5 defect 1)")
+
+    def cleanup(self):  # the launcher owns the process group; destroying it under live NCCL graphs blocks
+        if self.is_distributed and dist.is_initialized():
+            dist.barrier()
+        self._initialized = False
+
+    dm.DistributedManager.cleanup = cleanup
+    return rank != 0
 
 
 def main() -> None:

@@ -96,8 +96,34 @@ def install_executor() -> None:
     def _prepare_decode_input(self, sequences):
         return _hot(self).prepare_decode(sequences)
 
+    orig_initialize = cls.initialize
+    orig_execute_batch = cls.execute_batch
+
+    def initialize(self, max_num_batched_tokens: int, max_num_seqs: int) -> None:
+        orig_initialize(self, max_num_batched_tokens, max_num_seqs)
+        # graphs on EVERY rank: the reference captures on rank 0 only (model_runner.py:113-115), which cannot
+        # work once the captured forward holds collectives
+        if torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1:
+            self.capture_device_graphs(max_num_seqs)
+
+    def execute_batch(self, sequences, prefill: bool = True):
+        tp_worker = torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1 \
+            and torch.distributed.get_rank() != 0
+        if not tp_worker or not sequences:
+            return orig_execute_batch(self, sequences, prefill)
+        # ParallelLMHead gathers the logits on rank 0 and returns None elsewhere (embed_head.py:217-229): workers
+        # run the same forward (their half of every collective) and sample nothing
+        ref_ctx = importlib.import_module("minivllm.utils.context")
+        try:
+            input_ids, positions = self._prepare_batch_input(sequences, prefill)
+            self._execute_model(input_ids, positions, prefill)
+            self.inference_count += 1
+            return None, []
+        finally:
+            ref_ctx.reset_context()
+
     def capture_device_graphs(self, max_batch_size: int) -> None:
-        if self.enforce_eager or self.device.type != "cuda":
+        if self.enforce_eager or self.device.type != "cuda" or self.graphs:
             return
         hot = _hot(self)
         with torch.inference_mode(False):
@@ -109,9 +135,11 @@ def install_executor() -> None:
         if out is None:
             return self._execute_eager(input_ids, positions)
         with torch.inference_mode():
-            return self.model.compute_logits(out)
+            return self.model.compute_logits(out)  # None on TP workers
 
     cls.__init__ = __init__
+    cls.initialize = initialize
+    cls.execute_batch = execute_batch
     cls._prepare_prefill_input = _prepare_prefill_input
     cls._prepare_decode_input = _prepare_decode_input
     cls.capture_device_graphs = capture_device_graphs

@@ -70,18 +70,20 @@ def locate_reference() -> str | None:
     return None
 
 
-def import_reference(device: str = "cpu", *, hide_flash_attn: bool = True):
+def import_reference(device: str = "cpu", *, hide_flash_attn: bool = True, isolate_cuda: bool = True):
     """Import the reference package for ``device`` ('cpu' | 'cuda') and return the module.
 
     ``colorama`` is the reference's only dependency missing from the image: a blank stand-in is
     registered.  ``hide_flash_attn`` forces the reference's own eager attention branch
     (attention.py:80-87,450-453); it is irrelevant once ``install_into_reference()`` has swapped the layer.
+    ``MINIVLLM_DEVICE`` is read by the reference at call time (utils/device.py:74-78), so one process may
+    run a CPU engine and a CUDA engine one after the other.
     """
     root = locate_reference()
     if root is None:
         raise RuntimeError("reference not found: neither /root/reference nor oracle/_ref/ (run oracle/make_ref.py)")
     os.environ["MINIVLLM_DEVICE"] = device
-    if device == "cpu":
+    if device == "cpu" and isolate_cuda:  # bench.py times the CPU path inside a process that also drives the GPU
         os.environ["CUDA_VISIBLE_DEVICES"] = ""
     if "colorama" not in sys.modules:
         shim = types.ModuleType("colorama")
@@ -114,12 +116,47 @@ def seeded_tensor(name: str, shape, seed: int = 1234):
 
 
 def seeded_load(model, path=None) -> None:
-    """Stands in for ``load_model`` (utils/loader.py:90-239)."""
-    import torch  # noqa: PLC0415
+    """Stands in for ``load_model`` (utils/loader.py:90-239).
 
+    Under tensor parallelism every rank draws the FULL tensor of each parameter (same name -> same values as
+    at TP=1) and hands it to the reference's own ``weight_loader`` of that parameter (linear.py:146-270,
+    embed_head.py:106-119), which keeps this rank's shard — so a TP=N engine holds exactly the TP=1 weights."""
+    import torch  # noqa: PLC0415
+    import torch.distributed as dist  # noqa: PLC0415
+
+    tp = dist.get_world_size() if dist.is_initialized() else 1
     with torch.no_grad():
-        for name, param in model.named_parameters():
-            param.copy_(seeded_tensor(name, tuple(param.shape)).to(param.dtype))
+        if tp == 1:
+            for name, param in model.named_parameters():
+                param.copy_(seeded_tensor(name, tuple(param.shape)).to(param.dtype))
+            return
+        seen: set[int] = set()
+        for mod_name, mod in model.named_modules():
+            for pname, param in mod.named_parameters(recurse=False):
+                if id(param) in seen:  # tied lm_head / embedding
+                    continue
+                seen.add(id(param))
+                name = f"{mod_name}.{pname}" if mod_name else pname
+                cls = type(mod).__name__
+                shape = list(param.shape)
+                dt = param.dtype
+                if cls == "QKVParallelLinear":
+                    q, kv = mod.num_heads * tp * mod.head_size, mod.num_kv_heads * tp * mod.head_size
+                    shape[0] = q + 2 * kv
+                    for sid, part in zip("qkv", seeded_tensor(name, shape).split([q, kv, kv], 0)):
+                        param.weight_loader(param, part.to(dt), sid)
+                elif cls == "MergedColumnParallelLinear":
+                    shape[0] = sum(mod.output_sizes)
+                    for i, part in enumerate(seeded_tensor(name, shape).split(list(mod.output_sizes), 0)):
+                        param.weight_loader(param, part.to(dt), i)
+                elif cls in ("VocabParallelEmbedding", "ParallelLMHead"):
+                    shape[0] *= tp
+                    param.weight_loader(param, seeded_tensor(name, shape).to(dt))
+                elif getattr(mod, "tp_dim", None) is not None and param.dim() > mod.tp_dim:
+                    shape[mod.tp_dim] *= tp
+                    param.weight_loader(param, seeded_tensor(name, shape).to(dt))
+                else:  # replicated: norms, row-parallel biases
+                    param.copy_(seeded_tensor(name, tuple(param.shape)).to(dt))
 
 
 def fast_device_load(device: str, dtype_name: str, seed: int = 1234):

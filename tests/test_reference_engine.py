@@ -10,8 +10,8 @@ eager CPU engine on the NAMED architectures (Qwen3-0.6B dims, 28 layers, 151 936
 dims = BASELINE config 1) with seeded random weights, 32 greedy tokens per prompt.  Bars:
 
 * float32: token-for-token equal.  The only tolerated difference is a proven near-tie — the reference's own
-  top-2 logits at that step differ by < 2e-4 and the GPU picked the runner-up (GPU and CPU GEMMs sum in a
-  different order); the number of such steps is printed and must stay <= 1 per case.
+  top-2 logits at that step differ by < 2e-4 and the GPU picked the other of those two candidates (GPU and
+  CPU GEMMs sum in a different order); the number of such steps is printed and must stay <= 1 per case.
 * bfloat16: same rule with the near-tie bound at 4 bf16 ulps of the logit (0.0625); the stream is compared up
   to the first tolerated divergence (free-running generation cannot be compared after it).
 * call B's prompts share 2-3 leading blocks with call A's: on the one GPU engine they HIT the prefix cache
@@ -64,7 +64,9 @@ def _compare(tag: str, info: dict, tie_gap: float) -> dict:
                     report["max_top1_diff"] = max(report["max_top1_diff"], abs(res["top2"][i][t][0] - float(top2[t, 0])))
                     continue
                 gap = float(top2[t, 0] - top2[t, 1])
-                assert gap <= tie_gap and a == int(top2[t, 3]), (
+                # the reference itself samples through multinomial(softmax(logits / 1e-8)): on a tie it may have
+                # taken either of its two top candidates, so the GPU token must be one of those two
+                assert gap <= tie_gap and a in (int(top2[t, 2]), int(top2[t, 3])), (
                     f"{tag} call {call} prompt {i} step {t}: got {a}, reference {b} "
                     f"(reference top-2 gap {gap:.3e}, runner-up {int(top2[t, 3])})\n got  {got}\n want {want}")
                 report["near_ties"] += 1

@@ -106,3 +106,45 @@ def test_kv_head_sharding_needs_no_collective_inside_the_path():
             p.join(120)
         assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
         assert ret[0] < 1e-12 and ret[1] < 1e-12
+
+
+def _ref_engine_worker(rank: int, world: int, port: int, prompts, ret):
+    """The REFERENCE's own engine at TP=2 inside launcher-started ranks (what bench.py's engine leg does under
+    torchrun): process group first, then the model (defect 1), per-rank KV heads (defect 2), no spawn."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), LOCAL_RANK=str(rank),
+                      WORLD_SIZE=str(world), MINIVLLM_TP_BACKEND="gloo")
+    torch.set_num_threads(2)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from harness import ref_engine
+
+    info = ref_engine.run("tiny-qwen3", device="cpu", dtype="float32", executor=True, calls=[prompts], max_tokens=16,
+                          tensor_parallel_size=world, under_torchrun=True, max_num_seqs=8, max_model_len=1024,
+                          num_kvcache_blocks=64)
+    if rank == 0:
+        ret["tokens"] = info["calls"][0]["tokens"]
+        ret["kv_heads_rank0"] = info["kv_heads_per_rank"]
+    else:
+        ret["worker"] = bool(info.get("worker"))
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference/minivllm") and not os.path.isdir(
+    os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "minivllm")),
+    reason="needs the reference (or oracle/_ref)")
+def test_reference_engine_tp2_gloo_matches_its_single_rank_stream():
+    g = load_golden("engine")
+    n = int(g["tiny-qwen3.n"])
+    prompts = [g[f"tiny-qwen3.prompt{i}"].tolist() for i in range(n)]
+    want = [g[f"tiny-qwen3.tokens{i}"].tolist()[:16] for i in range(n)]
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_ref_engine_worker, args=(r, 2, port, prompts, ret)) for r in range(2)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(600)
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        assert ret["worker"] is True
+        assert ret["kv_heads_rank0"] == 1  # tiny-qwen3 has 2 KV heads: one per rank in the cache
+        assert ret["tokens"] == want
