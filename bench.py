@@ -50,6 +50,9 @@ WORKLOADS = {
                   batch=256, ctx=2048, ragged=(1024, 3072)),
     "cfg4": dict(name="Qwen2-7B decode 1 seq x 32768 ctx (split-KV stress), bf16, CUDA Graph", layers=28, H=28, KVH=4, D=128, batch=1, ctx=32768),
     "cfg5d": dict(name="Qwen2-72B TP8-rank decode 512 seqs x 1024 ctx, bf16, CUDA Graph", layers=80, H=8, KVH=1, D=128, batch=512, ctx=1024),
+    # per-rank shapes of the TP configurations, runnable on one GPU (what one of N ranks computes)
+    "cfg2tp8": dict(name="Qwen3-0.6B decode 256 seqs x 2048 ctx, ONE rank of TP8 (KVH 1), bf16, CUDA Graph", layers=28, H=2, KVH=1, D=128, batch=256, ctx=2048),
+    "cfg3d": dict(name="Qwen3-4B decode 8 seqs x 2304 ctx, bf16, CUDA Graph", layers=36, H=32, KVH=8, D=128, batch=8, ctx=2304),
     "tiny": dict(name="debug", layers=2, H=16, KVH=8, D=128, batch=8, ctx=512),
     # prefill workloads (metric: prefill attention TFLOP/s)
     "cfg3p": dict(name="Qwen3-4B prefill 8 seqs x (1024 cached + 1024 new), bf16, 50% prefix hits", kind="prefill",
@@ -453,12 +456,12 @@ def run_decode(env: Env, args, wl, wl_key) -> dict:
     v = torch.randn(B, KVH, D, device=dev).to(torch.bfloat16)
     splits = args.splits or m.ops.decode_num_splits(B, KVH, nblk * BLOCK, dev)
     ws_n = m.ops.decode_workspace_numel(B, H, D, splits)
-    workspace = torch.empty(max(ws_n, 1), dtype=torch.float32, device=dev)
+    workspace = m.ops.decode_workspace(ws_n, dev)
     outs = torch.empty(L, B, H, D, dtype=torch.bfloat16, device=dev)
 
     def set_ctx(sl=slot_mapping, cl=context_lens, bt=block_tables):
         m.set_context(False, slot_mapping=sl, context_lens=cl, block_tables=bt,
-                      decode_num_splits=splits, decode_workspace=workspace if splits > 1 else None)
+                      decode_num_splits=splits, decode_workspace=workspace)
 
     def full_step():  # the hot path of one decode step: store + paged decode, every layer
         for l, a in enumerate(layers):
@@ -467,7 +470,7 @@ def run_decode(env: Env, args, wl, wl_key) -> dict:
     def decode_only():
         for l, a in enumerate(layers):
             m.paged_decode_attention(q, a.k_cache, a.v_cache, block_tables, context_lens, scale,
-                                     num_splits=splits, workspace=workspace if splits > 1 else None, out=outs[l])
+                                     num_splits=splits, workspace=workspace, out=outs[l])
 
     def capture(fn):
         side = torch.cuda.Stream()
@@ -524,8 +527,7 @@ def run_decode(env: Env, args, wl, wl_key) -> dict:
 
     bytes_layer_rank = kv_bytes_per_layer(ctx_sum, KVH, D)
     bytes_step_job = bytes_layer_rank * L * tp
-    fused_reduce = "decode_tma_mma_fused" in kernels or any("fused" in x for x in kernels)
-    launches_per_step = L * (2 + (1 if splits > 1 and not fused_reduce else 0))
+    launches_per_step = L * 2  # store_kvcache + paged_decode (the split reduction is fused into the decode kernel)
     peaks = load_peaks()
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_layer_rank / (ms_dec / L * 1e-3) / 1e9
@@ -811,6 +813,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="default", choices=["default"] + sorted(WORKLOADS))
     ap.add_argument("--splits", type=int, default=0, help="override the KV split count (0 = library heuristic)")
+    ap.add_argument("--ctx", type=int, default=0, help="exploration: override the context length of a decode workload")
+    ap.add_argument("--batch", type=int, default=0, help="exploration: override the batch of a decode workload")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-prefill", action="store_true", help="default workload: skip the cfg3 prefill leg")
     ap.add_argument("--no-engine", action="store_true", help="default workload: skip the Qwen3-4B engine leg")
@@ -818,7 +822,9 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     default = args.workload == "default"
     wl_key = "cfg2" if default else args.workload
-    wl = WORKLOADS[wl_key]
+    wl = dict(WORKLOADS[wl_key])
+    if args.ctx or args.batch:
+        wl.update(ctx=args.ctx or wl["ctx"], batch=args.batch or wl["batch"], name=wl["name"] + f" [override ctx={args.ctx} batch={args.batch}]")
     if args.impl == "reference":
         run_reference_arm(args, wl)
         return

@@ -53,6 +53,7 @@ def run(
     tensor_parallel_size: int = 1,
     under_torchrun: bool = False,
     isolate_cuda: bool = True,
+    profile: str = "",
     **config_kw,
 ) -> dict:
     """Build one reference ``LLM`` and run ``generate`` once per entry of ``calls`` (later calls can hit the
@@ -144,7 +145,16 @@ def run(
         top_log.clear()
         hits0 = llm.scheduler.block_manager.stats.get("cache_hits", 0)
         t0 = time.perf_counter()
-        res = llm.generate(prompts, sp, use_tqdm=False)
+        if profile and ci == len(calls) - 1:
+            from torch.profiler import ProfilerActivity, profile as torch_profile
+
+            with torch_profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as prof:
+                res = llm.generate(prompts, sp, use_tqdm=False)
+            with open(profile, "w") as f:
+                f.write(prof.key_averages().table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=80))
+                f.write("\n\n" + prof.key_averages().table(sort_by="self_cpu_time_total", row_limit=30, max_name_column_width=80))
+        else:
+            res = llm.generate(prompts, sp, use_tqdm=False)
         sync()
         wall = time.perf_counter() - t0
         pre = [(n, t) for n, t in steps if n > 0]

@@ -36,7 +36,7 @@ extern "C" {
 #define MVB200_API
 #endif
 
-#define MVB200_VERSION 110
+#define MVB200_VERSION 120
 
 /* element types */
 #define MVB200_F32 0
@@ -86,12 +86,21 @@ MVB200_API int mvb200_store_kvcache(const void* key, const void* value,
  * Rows with context_lens[b] <= 0 produce zeros.  Block-table entries that are negative inside
  * the context contribute a zero key/value row (the eager reference's behaviour).
  *
- * num_splits >= 1 partitions every sequence's KV range over that many CTAs (grid is independent
- * of the data, as CUDA Graph replay needs).  When num_splits > 1, `workspace` must hold
- * mvb200_decode_workspace_bytes(B, H, D, num_splits) bytes; a second kernel reduces the splits.
+ * num_splits >= 1 partitions every sequence's KV range into that many work units (the grid is
+ * persistent and independent of the data, as CUDA Graph replay needs).  The CTA that finishes the last
+ * split of a (sequence, kv head) combines the partials: one kernel, no separate reduction launch.
+ *
+ * workspace: mvb200_decode_workspace_bytes(B, H, D, num_splits) bytes, 16-byte aligned, size a multiple
+ * of 16, prepared ONCE with mvb200_decode_workspace_init (which zeroes the arrival tickets and the work
+ * counter kept in the LAST bytes of the buffer and stamps it; the kernel re-arms them itself, so the same
+ * buffer serves every later call, any batch size or split count it is large enough for — always pass the
+ * same workspace_bytes).  One workspace per stream: two launches in flight must not share one.
+ * Required when num_splits > 1.  With num_splits == 1 it is optional: without it the units are dealt
+ * round-robin instead of being drawn from the device-side counter (ragged batches balance worse).
  */
 MVB200_API size_t mvb200_decode_workspace_bytes(int32_t batch, int32_t num_heads, int32_t head_dim,
                                      int32_t num_splits);
+MVB200_API int mvb200_decode_workspace_init(void* workspace, size_t workspace_bytes, void* stream);
 
 /* Split count the library recommends for a batch (>=1). max_context bounds the longest sequence. */
 MVB200_API int32_t mvb200_decode_suggest_splits(int32_t batch, int32_t num_kv_heads, int32_t max_context,

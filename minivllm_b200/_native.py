@@ -30,6 +30,7 @@ SIGNATURES = {
     ),
     "mvb200_decode_workspace_bytes": (c_size_t, [c_int32, c_int32, c_int32, c_int32]),
     "mvb200_decode_suggest_splits": (c_int32, [c_int32, c_int32, c_int32, c_int32]),
+    "mvb200_decode_workspace_init": (c_int32, [c_void_p, c_size_t, c_void_p]),
     "mvb200_paged_decode": (
         c_int32,
         [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,

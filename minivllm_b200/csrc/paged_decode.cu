@@ -4,15 +4,19 @@
 // the eager PageAttention.__call__ (minivllm/models/layers/page_attention.py:35-133).
 //
 // Fast path (16-bit K/V, D in {64,128}, block_size % 64 == 0, group <= 16):
-//   grid = (KVH, num_splits, B); one CTA streams the 64-token tiles of ONE kv head of ONE
-//   sequence split.  A producer warp turns block-table entries into TMA coordinates and issues
-//   cp.async.bulk.tensor loads of whole K and V tiles (64 tokens x D, 128B-swizzled) into a
-//   multi-stage shared-memory ring guarded by full/empty mbarriers.  Four consumer warps each
-//   own 16 tokens of a tile: Q(group padded to 16 rows) x K^T and P x V run on mma.sync
-//   m16n8k16 with ldmatrix-fed fragments (K/V are read from HBM once per kv head, not once per
-//   query head), online softmax in fp32 with quad shuffles, exp2 with the scale folded in.
-//   Warps are merged through shared memory at the end; with num_splits > 1 each CTA writes a
-//   normalised partial + log-sum-exp and decode_reduce_kernel combines them.
+//   Work unit = (sequence, KV split, kv head).  The grid is PERSISTENT: two resident CTAs per SM draw
+//   units from a device-side counter (kv head fastest, so co-resident CTAs read adjacent 256-byte
+//   segments of the same token rows) until none is left.  Per CTA a producer warp turns block-table
+//   entries into TMA coordinates and issues cp.async.bulk.tensor loads of whole K and V tiles (64 tokens
+//   x D, 128B-swizzled) into a multi-stage shared-memory ring guarded by full/empty mbarriers; the ring
+//   keeps streaming across unit boundaries (the unit's Q rows ride along as a 1-D bulk copy).  Four
+//   consumer warps each own 16 tokens of a tile: Q(group padded to 16 rows) x K^T and P x V run on
+//   mma.sync m16n8k16 with ldmatrix-fed fragments (K/V are read from HBM once per kv head, not once per
+//   query head), online softmax in fp32 with quad shuffles, exp2 with the scale folded in.  At the end
+//   of a unit the warps merge through a ring slot the producer lends them.  With num_splits > 1 each
+//   unit writes a normalised partial + log-sum-exp and counts itself on the ticket of its (sequence, kv
+//   head); once the units run out the same CTAs draw (sequence, head) rows from a second counter and
+//   combine each row's partials as soon as its ticket is complete (no second kernel, no launch gap).
 //   HBM-bound: algorithmic bytes = ctx * D * 2 (K,V) * elem per (sequence, kv head).
 //
 // Generic path (fp32 caches, any D <= 256, any block size, any group): one CTA per (b, h),
@@ -25,12 +29,23 @@
 namespace mvb200 {
 
 // =============================================================================================
-// fast path
+// fast path: persistent CTAs over (sequence, split, kv head) units, fused split reduction
 // =============================================================================================
 
 constexpr int kTileTokens = 64;
 constexpr int kConsumerWarps = 4;
+constexpr int kConsumerThreads = kConsumerWarps * 32;
 constexpr int kDecodeThreads = (kConsumerWarps + 1) * 32;
+constexpr int kMaxGroup = 16;
+constexpr int kQSlotBytes = kMaxGroup * 128 * 2;  // Q of one unit: up to 16 rows x 128 x 16 bit
+
+// Persistent part of the workspace (the LAST kDecodeTailBytes of the caller's buffer, at the same place
+// for every batch size / split count that shares the buffer): one arrival ticket per (sequence, kv head)
+// and the dynamic work counters.  Zeroed once by mvb200_decode_workspace_init; the kernel leaves it zeroed.
+constexpr int kDecodeMaxTickets = 65536;
+constexpr int kSchedInts = 16;  // [0] next unit, [1] CTAs past their last unit, [3] cookie, [4]/[5] same for reduce rows
+constexpr uint32_t kWorkspaceCookie = 0x6d766232u;
+constexpr size_t kDecodeTailBytes = (size_t)kDecodeMaxTickets * 4 + kSchedInts * 4;
 
 struct DecodeParams {
   const void* q;
@@ -40,18 +55,45 @@ struct DecodeParams {
   const int32_t* context_lens;
   void* out;
   int64_t out_row_stride;
-  float* part_o;    // [B, H, S, D]
-  float* part_lse;  // [B, H, S]  (log2 domain)
+  float* part_o;     // [B, H, S, D]
+  float* part_lse;   // [B, H, S]  (log2 domain)
+  int32_t* tickets;  // [B * KVH] arrivals of a (sequence, kv head)'s splits; nullptr when num_splits == 1
+  int32_t* sched;    // dynamic unit counter (nullptr: static round-robin over the grid)
+  int32_t batch;
   int32_t num_heads;
   int32_t num_kv_heads;
   int32_t group;
-  int32_t max_blocks;      // block-table width (MB)
+  int32_t max_blocks;       // block-table width (MB)
   int32_t tiles_per_block;  // block_size / 64
   int32_t num_blocks;       // NB (also the out-of-bounds TMA coordinate -> zero fill)
   int32_t num_splits;
   int32_t stages;
+  int32_t total_units;  // B * num_splits * KVH
+  int32_t q_bulk;       // Q rows of a unit can be fetched with one 16-byte-aligned bulk copy
   float scale_log2;
 };
+
+// What the producer tells the consumer warps about a unit (written to shared memory before the `full`
+// arrival of the unit's first ring slot).
+struct __align__(16) UnitInfo {
+  int32_t b, kvh, split, t0;
+  int32_t n;  // tiles of the unit; -1 = no more units
+  int32_t ctx;
+  int32_t pad[2];
+};
+
+MVB_DEV void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar)
+      : "memory");
+}
+MVB_DEV void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
+MVB_DEV float ld_cg_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
 
 template <typename T, int D>
 __global__ void __launch_bounds__(kDecodeThreads)
@@ -62,25 +104,30 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
   constexpr int kTileBytes = kHalves * kHalfBytes;      // K (or V) tile
   constexpr int kStageBytes = 2 * kTileBytes;           // K + V
   constexpr int kKSteps = D / 16;
+  static_assert(kConsumerWarps * kMaxGroup * D * 4 <= kStageBytes, "merge scratch must fit the ring slot it borrows");
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // dynamic smem base is only guaranteed 16B aligned: round up to the swizzle atom
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const int stages = p.stages;
-  const uint32_t bar_base = smem_base + stages * kStageBytes;  // full[stages], empty[stages]
+  // layout: ring[stages] | q[stages] | full[stages] empty[stages] | UnitInfo[stages] | mm[64] ml[64]
+  const uint32_t q_base = smem_base + stages * kStageBytes;
+  const uint32_t bar_base = q_base + stages * kQSlotBytes;
+  UnitInfo* uinfo = reinterpret_cast<UnitInfo*>(smem_gen + (bar_base - smem_base) + 16 * stages);
+  float* mm = reinterpret_cast<float*>(uinfo + stages);  // [4][16] running max of each warp's rows
+  float* ml = mm + kConsumerWarps * kMaxGroup;           // [4][16] running sum
 
-  const int kvh = blockIdx.x;
-  const int split = blockIdx.y;
-  const int b = blockIdx.z;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int G = p.group;
+  const int S = p.num_splits;
+  const int KVH = p.num_kv_heads;
 
   // prologue that needs nothing from earlier kernels runs before the dependency wait (PDL)
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) {
-      mbar_init(bar_base + 8 * s, 1);                           // full: producer's expect_tx arrive
+      mbar_init(bar_base + 8 * s, 1);                           // full: producer's (expect_tx) arrive
       mbar_init(bar_base + 8 * (stages + s), kConsumerWarps);   // empty: one arrive per warp
     }
     fence_mbar_init();
@@ -91,247 +138,416 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
   }
   __syncthreads();
   pdl_wait();               // q, context_lens, block tables and the freshly stored K/V are visible from here
-  pdl_launch_dependents();  // the split reduction (or the next layer's kernel) may start its own prologue
-
-  const int ctx = p.context_lens[b];
-  const int n_tiles = ctx > 0 ? (ctx + kTileTokens - 1) / kTileTokens : 0;
-  const int tps = (n_tiles + p.num_splits - 1) / p.num_splits;
-  const int t0 = split * tps;
-  const int t1 = min(n_tiles, t0 + tps);
+  pdl_launch_dependents();  // the next kernel may start its own prologue
 
   T* out = reinterpret_cast<T*>(p.out);
-  if (t1 <= t0) {
-    // empty split (or padded row with context_len == 0): publish "no contribution"
-    if (p.num_splits > 1) {
-      for (int r = threadIdx.x; r < G; r += blockDim.x) {
-        const int h = kvh * G + r;
-        p.part_lse[((int64_t)b * p.num_heads + h) * p.num_splits + split] = -INFINITY;
+
+  if (warp == kConsumerWarps) {
+    // ------------------------------ producer warp ------------------------------
+    // Walks this CTA's units back to back: the ring keeps streaming across unit boundaries, so the
+    // consumers' merge / write-out of one unit overlaps the loads of the next (no per-CTA prologue and
+    // no wave tail as with one CTA per unit).  Ring entries of a unit: its n tiles, then one slot that
+    // carries no data and is lent to the consumers as merge scratch.
+    if (p.sched != nullptr && blockIdx.x == 0 && lane == 0 &&
+        reinterpret_cast<volatile uint32_t*>(p.sched)[3] != kWorkspaceCookie) {
+      printf("mvb200: decode workspace was not initialised (mvb200_decode_workspace_init)\n");
+      __trap();
+    }
+    int it = 0;
+    // The first unit is the CTA's own index (no round trip to the counter before the first load); the next
+    // one is drawn when a unit STARTS, so the atomic's latency hides behind that unit's tiles.  The counter
+    // therefore counts draws beyond the first round.
+    int u = blockIdx.x;
+    for (;;) {
+      if (u >= p.total_units) {
+        if (lane == 0) {
+          const int s = it % stages;
+          mbar_wait(bar_base + 8 * (stages + s), ((it / stages) & 1) ^ 1);
+          uinfo[s].n = -1;
+          mbar_arrive(bar_base + 8 * s);
+          if (p.sched != nullptr) {
+            // every CTA draws exactly one out-of-range unit: the last one to do so re-arms the counters
+            const int done = atomicAdd(p.sched + 1, 1);
+            if (done == (int)gridDim.x - 1) {
+              p.sched[0] = 0;
+              p.sched[1] = 0;
+              __threadfence();
+            }
+          }
+        }
+        break;
       }
-    } else {
-      for (int i = threadIdx.x; i < G * D; i += blockDim.x)
-        out[(int64_t)b * p.out_row_stride + (int64_t)kvh * G * D + i] = from_f32<T>(0.f);
+      int u_next = 0;
+      if (lane == 0) u_next = p.sched != nullptr ? (int)gridDim.x + atomicAdd(p.sched, 1) : u + (int)gridDim.x;
+      const int kvh = u % KVH;
+      const int rest = u / KVH;
+      const int split = rest % S;
+      const int b = rest / S;
+      const int ctx = __ldg(p.context_lens + b);
+      const int n_tiles = ctx > 0 ? (ctx + kTileTokens - 1) / kTileTokens : 0;
+      const int tps = (n_tiles + S - 1) / S;
+      const int t0 = split * tps;
+      const int t1 = min(n_tiles, t0 + tps);
+      const int n = max(t1 - t0, 0);
+      const int32_t* bt = p.block_tables + (int64_t)b * p.bt_row_stride;
+      const uint32_t q_bytes = (uint32_t)(G * D * (int)sizeof(T));
+      for (int base = 0; base < n; base += 32) {
+        // 32 block-table entries per coalesced load, then one lane issues the copies
+        int my_bid = p.num_blocks;  // out-of-bounds coordinate: TMA fills the tile with zeros
+        int my_sub = 0;
+        if (base + lane < n) {
+          const int t = t0 + base + lane;
+          const int j = min(t / p.tiles_per_block, p.max_blocks - 1);  // page_attention.py:83-84
+          const int v = __ldg(bt + j);
+          if (v >= 0 && v < p.num_blocks) my_bid = v;
+          my_sub = (t % p.tiles_per_block) * kTileTokens;
+        }
+        const int cnt = min(32, n - base);
+        for (int i = 0; i < cnt; ++i) {
+          const int bid = __shfl_sync(0xffffffffu, my_bid, i);
+          const int sub = __shfl_sync(0xffffffffu, my_sub, i);
+          if (lane == 0) {
+            const int s = it % stages;
+            const uint32_t full = bar_base + 8 * s;
+            mbar_wait(bar_base + 8 * (stages + s), ((it / stages) & 1) ^ 1);
+            const bool first = base + i == 0;
+            if (first) uinfo[s] = UnitInfo{b, kvh, split, t0, n, ctx, {0, 0}};
+            mbar_arrive_expect_tx(full, kStageBytes + (first && p.q_bulk ? q_bytes : 0u));
+            if (first && p.q_bulk)
+              bulk_load_1d(q_base + s * kQSlotBytes,
+                           reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_row_stride + (int64_t)kvh * G * D,
+                           q_bytes, full);
+            const uint32_t kdst = smem_base + s * kStageBytes;
+            const uint32_t vdst = kdst + kTileBytes;
+#pragma unroll
+            for (int h = 0; h < kHalves; ++h) {
+              tma_load_4d(kdst + h * kHalfBytes, &tmap_k, full, h * 64, kvh, sub, bid);
+              tma_load_4d(vdst + h * kHalfBytes, &tmap_v, full, h * 64, kvh, sub, bid);
+            }
+          }
+          ++it;
+          __syncwarp();
+        }
+      }
+      // the scratch slot: a ring entry without data (4 warps x G rows x D floats = 16 G D bytes never
+      // exceed a stage of 256 D bytes at G <= 16)
+      if (lane == 0) {
+        const int s = it % stages;
+        mbar_wait(bar_base + 8 * (stages + s), ((it / stages) & 1) ^ 1);
+        if (n == 0) uinfo[s] = UnitInfo{b, kvh, split, t0, 0, ctx, {0, 0}};
+        mbar_arrive(bar_base + 8 * s);
+      }
+      ++it;
+      __syncwarp();
+      u = __shfl_sync(0xffffffffu, u_next, 0);
     }
     return;
   }
 
-  // per-warp running state (consumer warps only)
-  float o_acc[D / 8][4];
-  float m_run[2] = {-INFINITY, -INFINITY};
-  float l_run[2] = {0.f, 0.f};
-
-  if (warp == kConsumerWarps) {
-    // ------------------------------ producer warp ------------------------------
-    const int n = t1 - t0;
-    const int32_t* bt = p.block_tables + (int64_t)b * p.bt_row_stride;
-    for (int base = 0; base < n; base += 32) {
-      // 32 block-table entries per coalesced load, then one lane issues the copies
-      int my_bid = p.num_blocks;  // out-of-bounds coordinate: TMA fills the tile with zeros
-      int my_sub = 0;
-      if (base + lane < n) {
-        const int t = t0 + base + lane;
-        const int j = min(t / p.tiles_per_block, p.max_blocks - 1);  // page_attention.py:83-84
-        const int v = __ldg(bt + j);
-        if (v >= 0 && v < p.num_blocks) my_bid = v;
-        my_sub = (t % p.tiles_per_block) * kTileTokens;
-      }
-      const int cnt = min(32, n - base);
-      for (int i = 0; i < cnt; ++i) {
-        const int bid = __shfl_sync(0xffffffffu, my_bid, i);
-        const int sub = __shfl_sync(0xffffffffu, my_sub, i);
-        if (lane == 0) {
-          const int it = base + i;
-          const int s = it % stages;
-          const uint32_t full = bar_base + 8 * s;
-          const uint32_t empty = bar_base + 8 * (stages + s);
-          mbar_wait(empty, ((it / stages) & 1) ^ 1);
-          mbar_arrive_expect_tx(full, kStageBytes);
-          const uint32_t kdst = smem_base + s * kStageBytes;
-          const uint32_t vdst = kdst + kTileBytes;
-#pragma unroll
-          for (int h = 0; h < kHalves; ++h) {
-            tma_load_4d(kdst + h * kHalfBytes, &tmap_k, full, h * 64, kvh, sub, bid);
-            tma_load_4d(vdst + h * kHalfBytes, &tmap_v, full, h * 64, kvh, sub, bid);
-          }
-        }
-        __syncwarp();
-      }
+  // ------------------------------ consumer warps -----------------------------
+  const int ctid = threadIdx.x;  // 0..127
+  // ldmatrix lane geometry (see DESIGN.md "decode fragment map")
+  const int krow = 16 * warp + (lane & 7) + ((lane >> 4) << 3);
+  const int ksel = (lane >> 3) & 1;
+  const int vrow = 16 * warp + (lane & 7) + (((lane >> 3) & 1) << 3);
+  const int vsel = lane >> 4;
+  int it = 0;
+  for (;;) {
+    {
+      const int s = it % stages;
+      mbar_wait(bar_base + 8 * s, (it / stages) & 1);
     }
-  } else {
-    // ------------------------------ consumer warps -----------------------------
+    const UnitInfo info = uinfo[it % stages];
+    if (info.n < 0) break;
+    const int b = info.b, kvh = info.kvh, split = info.split, t0 = info.t0, n = info.n, ctx = info.ctx;
+
+    float o_acc[D / 8][4];
+    float m_run[2] = {-INFINITY, -INFINITY};
+    float l_run[2] = {0.f, 0.f};
 #pragma unroll
     for (int i = 0; i < D / 8; ++i) o_acc[i][0] = o_acc[i][1] = o_acc[i][2] = o_acc[i][3] = 0.f;
 
-    // Q fragments (A operand, 16 x D, rows >= group are zero), straight from global
-    uint32_t qf[kKSteps][4];
-    {
-      const T* qb = reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_row_stride + (int64_t)kvh * G * D;
-      const int g = lane >> 2, t = lane & 3;
+    if (n > 0) {
+      // Q fragments (A operand, 16 x D, rows >= group are zero): from the unit's Q slot, or from global
+      uint32_t qf[kKSteps][4];
+      {
+        const int g = lane >> 2, t = lane & 3;
+        if (p.q_bulk) {
+          const uint8_t* qs = smem_gen + (q_base - smem_base) + (it % stages) * kQSlotBytes;
 #pragma unroll
-      for (int kk = 0; kk < kKSteps; ++kk) {
-        const int c = kk * 16 + 2 * t;
-        qf[kk][0] = g < G ? *reinterpret_cast<const uint32_t*>(qb + g * D + c) : 0u;
-        qf[kk][1] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + c) : 0u;
-        qf[kk][2] = g < G ? *reinterpret_cast<const uint32_t*>(qb + g * D + c + 8) : 0u;
-        qf[kk][3] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + c + 8) : 0u;
-      }
-    }
-
-    const int n = t1 - t0;
-    // ldmatrix lane geometry (see DESIGN.md "decode fragment map")
-    const int krow = 16 * warp + (lane & 7) + ((lane >> 4) << 3);
-    const int ksel = (lane >> 3) & 1;
-    const int vrow = 16 * warp + (lane & 7) + (((lane >> 3) & 1) << 3);
-    const int vsel = lane >> 4;
-
-    for (int it = 0; it < n; ++it) {
-      const int s = it % stages;
-      const uint32_t full = bar_base + 8 * s;
-      const uint32_t empty = bar_base + 8 * (stages + s);
-      const uint32_t kbase = smem_base + s * kStageBytes;
-      const uint32_t vbase = kbase + kTileBytes;
-      const int tile_tok0 = (t0 + it) * kTileTokens;
-      const bool partial = tile_tok0 + kTileTokens > ctx;
-
-      mbar_wait(full, (it / stages) & 1);
-
-      // ---- S = Q K^T for this warp's 16 tokens ----
-      float sacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+          for (int kk = 0; kk < kKSteps; ++kk) {
+            const int c = (kk * 16 + 2 * t) * 2;
+            qf[kk][0] = g < G ? *reinterpret_cast<const uint32_t*>(qs + g * D * 2 + c) : 0u;
+            qf[kk][1] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qs + (g + 8) * D * 2 + c) : 0u;
+            qf[kk][2] = g < G ? *reinterpret_cast<const uint32_t*>(qs + g * D * 2 + c + 16) : 0u;
+            qf[kk][3] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qs + (g + 8) * D * 2 + c + 16) : 0u;
+          }
+        } else {
+          const T* qb = reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_row_stride + (int64_t)kvh * G * D;
 #pragma unroll
-      for (int kk = 0; kk < kKSteps; ++kk) {
-        const int cidx = kk * 2 + ksel;
-        const uint32_t addr = kbase + (cidx >> 3) * kHalfBytes + krow * 128 +
-                              (((cidx & 7) ^ (krow & 7)) << 4);
-        uint32_t kf[4];
-        ldmatrix_x4(kf, addr);
-        Mma16816<T>::run(sacc[0], qf[kk], kf[0], kf[1]);
-        Mma16816<T>::run(sacc[1], qf[kk], kf[2], kf[3]);
-      }
-
-      if (partial) {
-        // tokens >= ctx: score -> -inf (select, K garbage may be NaN) and V rows -> 0 (0*NaN)
-        const int valid = ctx - tile_tok0;  // 1..63 valid tokens in this tile
-        const int c = 16 * warp + 2 * (lane & 3);
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          if (c + 8 * j >= valid) sacc[j][0] = sacc[j][2] = -INFINITY;
-          if (c + 8 * j + 1 >= valid) sacc[j][1] = sacc[j][3] = -INFINITY;
-        }
-        const int first_bad = max(valid, 16 * warp);
-        for (int r = first_bad; r < 16 * warp + 16; ++r) {
-          if (lane < kHalves * 8) {
-            uint8_t* dst = smem_gen + (vbase - smem_base) + (lane >> 3) * kHalfBytes + r * 128 + (lane & 7) * 16;
-            *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+          for (int kk = 0; kk < kKSteps; ++kk) {
+            const int c = kk * 16 + 2 * t;
+            qf[kk][0] = g < G ? *reinterpret_cast<const uint32_t*>(qb + g * D + c) : 0u;
+            qf[kk][1] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + c) : 0u;
+            qf[kk][2] = g < G ? *reinterpret_cast<const uint32_t*>(qb + g * D + c + 8) : 0u;
+            qf[kk][3] = g + 8 < G ? *reinterpret_cast<const uint32_t*>(qb + (g + 8) * D + c + 8) : 0u;
           }
         }
-        fence_proxy_async_smem();  // generic writes before the next TMA refill of this slab
-        __syncwarp();
       }
 
-      // ---- online softmax (log2 domain) ----
-      float alpha[2];
+      for (int j = 0; j < n; ++j, ++it) {
+        const int s = it % stages;
+        const uint32_t full = bar_base + 8 * s;
+        const uint32_t empty = bar_base + 8 * (stages + s);
+        const uint32_t kbase = smem_base + s * kStageBytes;
+        const uint32_t vbase = kbase + kTileBytes;
+        const int tile_tok0 = (t0 + j) * kTileTokens;
+        const bool partial = tile_tok0 + kTileTokens > ctx;
+
+        if (j > 0) mbar_wait(full, (it / stages) & 1);
+
+        // ---- S = Q K^T for this warp's 16 tokens ----
+        float sacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+        for (int kk = 0; kk < kKSteps; ++kk) {
+          const int cidx = kk * 2 + ksel;
+          const uint32_t addr = kbase + (cidx >> 3) * kHalfBytes + krow * 128 +
+                                (((cidx & 7) ^ (krow & 7)) << 4);
+          uint32_t kf[4];
+          ldmatrix_x4(kf, addr);
+          Mma16816<T>::run(sacc[0], qf[kk], kf[0], kf[1]);
+          Mma16816<T>::run(sacc[1], qf[kk], kf[2], kf[3]);
+        }
+
+        if (partial) {
+          // tokens >= ctx: score -> -inf (select, K garbage may be NaN) and V rows -> 0 (0*NaN)
+          const int valid = ctx - tile_tok0;  // 1..63 valid tokens in this tile
+          const int c = 16 * warp + 2 * (lane & 3);
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {
+            if (c + 8 * jj >= valid) sacc[jj][0] = sacc[jj][2] = -INFINITY;
+            if (c + 8 * jj + 1 >= valid) sacc[jj][1] = sacc[jj][3] = -INFINITY;
+          }
+          const int first_bad = max(valid, 16 * warp);
+          for (int r = first_bad; r < 16 * warp + 16; ++r) {
+            if (lane < kHalves * 8) {
+              uint8_t* dst = smem_gen + (vbase - smem_base) + (lane >> 3) * kHalfBytes + r * 128 + (lane & 7) * 16;
+              *reinterpret_cast<uint4*>(dst) = make_uint4(0, 0, 0, 0);
+            }
+          }
+          fence_proxy_async_smem();  // generic writes before the next TMA refill of this slab
+          __syncwarp();
+        }
+
+        // ---- online softmax (log2 domain) ----
+        float alpha[2];
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          float mx = fmaxf(fmaxf(sacc[0][2 * r], sacc[0][2 * r + 1]),
+                           fmaxf(sacc[1][2 * r], sacc[1][2 * r + 1]));
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+          mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+          const float m_new = fmaxf(m_run[r], mx * p.scale_log2);
+          const float m_use = m_new == -INFINITY ? 0.f : m_new;
+          alpha[r] = exp2f(m_run[r] - m_use);
+          m_run[r] = m_new;
+          float sum = 0.f;
+#pragma unroll
+          for (int jj = 0; jj < 2; ++jj) {
+            sacc[jj][2 * r] = exp2f(sacc[jj][2 * r] * p.scale_log2 - m_use);
+            sacc[jj][2 * r + 1] = exp2f(sacc[jj][2 * r + 1] * p.scale_log2 - m_use);
+            sum += sacc[jj][2 * r] + sacc[jj][2 * r + 1];
+          }
+          l_run[r] = l_run[r] * alpha[r] + sum;
+        }
+#pragma unroll
+        for (int i = 0; i < D / 8; ++i) {
+          o_acc[i][0] *= alpha[0];
+          o_acc[i][1] *= alpha[0];
+          o_acc[i][2] *= alpha[1];
+          o_acc[i][3] *= alpha[1];
+        }
+
+        // ---- O += P V ----
+        uint32_t pf[4];
+        pf[0] = Mma16816<T>::pack(sacc[0][0], sacc[0][1]);
+        pf[1] = Mma16816<T>::pack(sacc[0][2], sacc[0][3]);
+        pf[2] = Mma16816<T>::pack(sacc[1][0], sacc[1][1]);
+        pf[3] = Mma16816<T>::pack(sacc[1][2], sacc[1][3]);
+#pragma unroll
+        for (int np = 0; np < D / 16; ++np) {
+          const int cidx = np * 2 + vsel;
+          const uint32_t addr = vbase + (cidx >> 3) * kHalfBytes + vrow * 128 +
+                                (((cidx & 7) ^ (vrow & 7)) << 4);
+          uint32_t vf[4];
+          ldmatrix_x4_trans(vf, addr);
+          Mma16816<T>::run(o_acc[2 * np], pf, vf[0], vf[1]);
+          Mma16816<T>::run(o_acc[2 * np + 1], pf, vf[2], vf[3]);
+        }
+
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty);
+      }
+
+      // finish row sums across the quad
 #pragma unroll
       for (int r = 0; r < 2; ++r) {
-        float mx = fmaxf(fmaxf(sacc[0][2 * r], sacc[0][2 * r + 1]),
-                         fmaxf(sacc[1][2 * r], sacc[1][2 * r + 1]));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-        const float m_new = fmaxf(m_run[r], mx * p.scale_log2);
-        const float m_use = m_new == -INFINITY ? 0.f : m_new;
-        alpha[r] = exp2f(m_run[r] - m_use);
-        m_run[r] = m_new;
-        float sum = 0.f;
-#pragma unroll
-        for (int j = 0; j < 2; ++j) {
-          sacc[j][2 * r] = exp2f(sacc[j][2 * r] * p.scale_log2 - m_use);
-          sacc[j][2 * r + 1] = exp2f(sacc[j][2 * r + 1] * p.scale_log2 - m_use);
-          sum += sacc[j][2 * r] + sacc[j][2 * r + 1];
-        }
-        l_run[r] = l_run[r] * alpha[r] + sum;
+        l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
+        l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
       }
-#pragma unroll
-      for (int i = 0; i < D / 8; ++i) {
-        o_acc[i][0] *= alpha[0];
-        o_acc[i][1] *= alpha[0];
-        o_acc[i][2] *= alpha[1];
-        o_acc[i][3] *= alpha[1];
-      }
-
-      // ---- O += P V ----
-      uint32_t pf[4];
-      pf[0] = Mma16816<T>::pack(sacc[0][0], sacc[0][1]);
-      pf[1] = Mma16816<T>::pack(sacc[0][2], sacc[0][3]);
-      pf[2] = Mma16816<T>::pack(sacc[1][0], sacc[1][1]);
-      pf[3] = Mma16816<T>::pack(sacc[1][2], sacc[1][3]);
-#pragma unroll
-      for (int np = 0; np < D / 16; ++np) {
-        const int cidx = np * 2 + vsel;
-        const uint32_t addr = vbase + (cidx >> 3) * kHalfBytes + vrow * 128 +
-                              (((cidx & 7) ^ (vrow & 7)) << 4);
-        uint32_t vf[4];
-        ldmatrix_x4_trans(vf, addr);
-        Mma16816<T>::run(o_acc[2 * np], pf, vf[0], vf[1]);
-        Mma16816<T>::run(o_acc[2 * np + 1], pf, vf[2], vf[3]);
-      }
-
-      __syncwarp();
-      if (lane == 0) mbar_arrive(empty);
+      // the unit's scratch slot: a ring entry without data
+      mbar_wait(bar_base + 8 * (it % stages), (it / stages) & 1);
     }
 
-    // finish row sums across the quad
+    // ------------------------------ merge the four warps ------------------------------
+    // scratch[w][row][d ^ ((row & 7) << 3)] in the borrowed slot (XOR keeps the float2 stores of the eight
+    // row groups of a warp off each other's banks)
+    float* mo = reinterpret_cast<float*>(smem_gen + (size_t)(it % stages) * kStageBytes);
+    {
+      const int g = lane >> 2, t = lane & 3;
 #pragma unroll
-    for (int r = 0; r < 2; ++r) {
-      l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 1);
-      l_run[r] += __shfl_xor_sync(0xffffffffu, l_run[r], 2);
-    }
-  }
-
-  // ------------------------------ merge the four warps ------------------------------
-  // every issued tile has been consumed, so the ring can be reused as scratch
-  __syncthreads();
-  constexpr int kRowF = D + 4;  // padded row (floats)
-  float* mo = reinterpret_cast<float*>(smem_gen);                       // [4][16][kRowF]
-  float* mm = mo + kConsumerWarps * 16 * kRowF;                         // [4][16]
-  float* ml = mm + kConsumerWarps * 16;                                 // [4][16]
-  if (warp < kConsumerWarps) {
-    const int g = lane >> 2, t = lane & 3;
+      for (int r = 0; r < 2; ++r) {
+        const int row = g + 8 * r;
+        if (row < G) {
+          float* dst = mo + (warp * G + row) * D;
 #pragma unroll
-    for (int r = 0; r < 2; ++r) {
-      const int row = g + 8 * r;
-      if (row < G) {
-        float* dst = mo + (warp * 16 + row) * kRowF;
-#pragma unroll
-        for (int i = 0; i < D / 8; ++i)
-          *reinterpret_cast<float2*>(dst + i * 8 + 2 * t) = make_float2(o_acc[i][2 * r], o_acc[i][2 * r + 1]);
-        if (t == 0) {
-          mm[warp * 16 + row] = m_run[r];
-          ml[warp * 16 + row] = l_run[r];
+          for (int i = 0; i < D / 8; ++i)
+            *reinterpret_cast<float2*>(dst + ((i ^ (row & 7)) << 3) + 2 * t) = make_float2(o_acc[i][2 * r], o_acc[i][2 * r + 1]);
+          if (t == 0) {
+            mm[warp * kMaxGroup + row] = m_run[r];
+            ml[warp * kMaxGroup + row] = l_run[r];
+          }
         }
       }
     }
+    consumer_sync();
+    for (int idx = ctid; idx < G * D; idx += kConsumerThreads) {
+      const int row = idx / D, d = idx - row * D;
+      const int ds = (((d >> 3) ^ (row & 7)) << 3) + (d & 7);
+      float M = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, mm[w * kMaxGroup + row]);
+      const float Ms = M == -INFINITY ? 0.f : M;
+      float L = 0.f, o = 0.f;
+#pragma unroll
+      for (int w = 0; w < kConsumerWarps; ++w) {
+        const float sc = exp2f(mm[w * kMaxGroup + row] - Ms);
+        L += ml[w * kMaxGroup + row] * sc;
+        o += mo[(w * G + row) * D + ds] * sc;
+      }
+      const float val = L > 0.f ? o / L : 0.f;
+      const int h = kvh * G + row;
+      if (S == 1) {
+        out[(int64_t)b * p.out_row_stride + (int64_t)h * D + d] = from_f32<T>(val);
+      } else {
+        const int64_t ph = ((int64_t)b * p.num_heads + h) * S + split;
+        p.part_o[ph * D + d] = val;
+        if (d == 0) p.part_lse[ph] = L > 0.f ? M + log2f(L) : -INFINITY;
+      }
+    }
+
+    if (S > 1) {
+      // publish: bar.sync orders the CTA's partial stores before thread 0, whose fence (cumulative) makes
+      // them visible device-wide before the ticket is counted
+      if (p.tickets != nullptr) {
+        consumer_sync();
+        if (ctid == 0) {
+          __threadfence();
+          atomicAdd(p.tickets + ((int64_t)b * KVH + kvh), 1);
+        }
+      }
+    }
+
+    // hand the borrowed slot back
+    consumer_sync();
+    if (lane == 0) mbar_arrive(bar_base + 8 * (stages + (it % stages)));
+    ++it;
   }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < G * D; idx += blockDim.x) {
-    const int row = idx / D, d = idx - row * D;
+
+  if (S == 1 || p.tickets == nullptr) return;  // no tickets: decode_reduce_kernel follows
+  // ------------------------------ phase 2: split reduction, same kernel ------------------------------
+  // Every consumer WARP now takes (sequence, head) rows — its own index first, then from a second counter —
+  // and combines a row's S partials as soon as all splits of its (sequence, kv head) have been counted on
+  // the ticket: the units were handed out in the same order, so the wait is short, and whoever still owes
+  // a partial is running, not queued behind this CTA (a CTA gets here only after every unit was drawn).
+  // Lanes cover head_dim with 16-byte loads, eight partial rows in flight per lane; no CTA-wide barrier.
+  // Tickets and counters are re-armed for the next launch by their last user.
+  constexpr int kVecs = D / 4;  // float4 per partial row (32 for D = 128)
+  const int total_rows = p.batch * p.num_heads;
+  const int total_warps = (int)gridDim.x * kConsumerWarps;
+  int r = warp * (int)gridDim.x + blockIdx.x;  // first row: static (spread over the SMs first), later ones from the counter
+  for (;;) {
+    if (r >= total_rows) {
+      if (lane == 0) {
+        const int done = atomicAdd(p.sched + 5, 1);  // every warp ends on exactly one out-of-range row
+        if (done == total_warps - 1) {
+          p.sched[4] = 0;
+          p.sched[5] = 0;
+          __threadfence();
+        }
+      }
+      break;
+    }
+    int r_next = 0;
+    if (lane == 0) r_next = total_warps + atomicAdd(p.sched + 4, 1);  // latency hides behind this row
+    const int b = r / p.num_heads, h = r % p.num_heads;
+    int32_t* ticket = p.tickets + b * KVH + h / G;
+    if (lane == 0) {
+      int seen;
+      do {
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(ticket) : "memory");
+        if (seen < S) __nanosleep(32);
+      } while (seen < S);
+    }
+    __syncwarp();
+    const int64_t ph = (int64_t)r * S;
+    // weights first (S <= 128: four per lane), so that the partial rows below are plain independent loads
+    float wl[4];
     float M = -INFINITY;
 #pragma unroll
-    for (int w = 0; w < kConsumerWarps; ++w) M = fmaxf(M, mm[w * 16 + row]);
-    const float Ms = M == -INFINITY ? 0.f : M;
-    float L = 0.f, o = 0.f;
+    for (int i = 0; i < 4; ++i) {
+      const int sp = lane + 32 * i;
+      wl[i] = sp < S ? __ldcg(p.part_lse + ph + sp) : -INFINITY;
+      M = fmaxf(M, wl[i]);
+    }
 #pragma unroll
-    for (int w = 0; w < kConsumerWarps; ++w) {
-      const float sc = exp2f(mm[w * 16 + row] - Ms);
-      L += ml[w * 16 + row] * sc;
-      o += mo[(w * 16 + row) * kRowF + d] * sc;
+    for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+    float W = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      wl[i] = wl[i] == -INFINITY ? 0.f : exp2f(wl[i] - M);  // an empty split has weight 0 (its row holds no data)
+      W += wl[i];
     }
-    const float val = L > 0.f ? o / L : 0.f;
-    const int h = kvh * G + row;
-    if (p.num_splits == 1) {
-      out[(int64_t)b * p.out_row_stride + (int64_t)h * D + d] = from_f32<T>(val);
-    } else {
-      const int64_t ph = ((int64_t)b * p.num_heads + h) * p.num_splits + split;
-      p.part_o[ph * D + d] = val;
-      if (d == 0) p.part_lse[ph] = L > 0.f ? M + log2f(L) : -INFINITY;
+    W = warp_sum(W);
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4* rows = reinterpret_cast<const float4*>(p.part_o + ph * D) + (lane < kVecs ? lane : 0);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int lim = min(32, S - 32 * i);
+#pragma unroll 16
+      for (int j = 0; j < lim; ++j) {
+        const float w = __shfl_sync(0xffffffffu, wl[i], j);
+        float4 v = __ldcg(rows + (int64_t)(32 * i + j) * kVecs);
+        if (w == 0.f) v = make_float4(0.f, 0.f, 0.f, 0.f);  // never-written row: whatever was read is dropped
+        acc.x += w * v.x;
+        acc.y += w * v.y;
+        acc.z += w * v.z;
+        acc.w += w * v.w;
+      }
     }
+    if (lane < kVecs) {
+      const float inv = W > 0.f ? 1.f / W : 0.f;
+      T* dst = out + (int64_t)b * p.out_row_stride + (int64_t)h * D + 4 * lane;
+      dst[0] = from_f32<T>(acc.x * inv);
+      dst[1] = from_f32<T>(acc.y * inv);
+      dst[2] = from_f32<T>(acc.z * inv);
+      dst[3] = from_f32<T>(acc.w * inv);
+    }
+    if (lane == 0) {
+      const int old = atomicAdd(ticket, 1);
+      if (old == S + G - 1) *ticket = 0;  // all S splits counted and all G rows combined: re-arm
+    }
+    r = __shfl_sync(0xffffffffu, r_next, 0);
   }
 }
 
@@ -386,6 +602,9 @@ decode_reduce_kernel(const float* __restrict__ part_o, const float* __restrict__
     out[(int64_t)b * out_row_stride + (int64_t)h * head_dim + d] = from_f32<T>(W > 0.f ? o / W : 0.f);
   }
 }
+
+
+__global__ void decode_workspace_init_kernel(uint32_t* sched) { sched[3] = kWorkspaceCookie; }
 
 // =============================================================================================
 // generic path: one CTA (4 warps) per (sequence, query head); any dtype / head_dim / block size
@@ -466,9 +685,30 @@ paged_decode_generic_kernel(const T* __restrict__ q, int64_t q_row_stride,
 // host launchers
 // =============================================================================================
 
+static int decode_ctas_per_sm() {
+  static int v = 0;
+  if (!v) {
+    const char* e = getenv("MVB200_DECODE_CTAS_PER_SM");
+    v = e ? atoi(e) : 2;
+    if (v < 1) v = 1;
+    if (v > 2) v = 2;
+  }
+  return v;
+}
+
+// MVB200_DECODE_REDUCE = fused | kernel: combine the split partials inside the persistent kernel (phase 2)
+// or with decode_reduce_kernel launched behind it (PDL).
+static bool decode_fused_reduce() {
+  static const bool v = [] {
+    const char* e = getenv("MVB200_DECODE_REDUCE");
+    return !(e && e[0] == 'k');
+  }();
+  return v;
+}
+
 template <typename T, int D>
-static int launch_fast(const DecodeParams& p, const void* k_cache, const void* v_cache,
-                       int block_size, int batch, cudaStream_t stream) {
+static int launch_fast(DecodeParams& p, const void* k_cache, const void* v_cache,
+                       int block_size, cudaStream_t stream) {
   CUtensorMap mk, mv;
   const uint64_t dims[4] = {(uint64_t)D, (uint64_t)p.num_kv_heads, (uint64_t)block_size,
                             (uint64_t)p.num_blocks};
@@ -481,30 +721,30 @@ static int launch_fast(const DecodeParams& p, const void* k_cache, const void* v
   if (rc) return rc;
 
   constexpr int kStageBytes = 2 * (D / 64) * kTileTokens * 128;
-  const int merge_bytes = (kConsumerWarps * 16 * (D + 4) + 2 * kConsumerWarps * 16) * 4;
-  int smem = p.stages * kStageBytes + 2 * p.stages * 8;
-  if (smem < merge_bytes) smem = merge_bytes;
-  smem += 1024;  // alignment slack
+  // ring | Q slots | barriers | unit info | per-warp max/sum | alignment slack
+  const int smem = p.stages * (kStageBytes + kQSlotBytes) + p.stages * (16 + (int)sizeof(UnitInfo)) +
+                   2 * kConsumerWarps * kMaxGroup * 4 + 1024;
   auto kern = paged_decode_kernel<T, D>;
   static SmemOptIn optin;
   rc = optin_dynamic_smem((const void*)kern, smem, &optin, "paged_decode");
   if (rc) return rc;
-  dim3 grid(p.num_kv_heads, p.num_splits, batch);
-  cudaError_t le = launch_pdl(kern, grid, dim3(kDecodeThreads), (size_t)smem, stream, mk, mv, p);
+  // persistent grid: the CTAs that can be resident at once, or one per unit when there are fewer units
+  int64_t ctas = (int64_t)decode_ctas_per_sm() * device_sm_count();
+  if (ctas > p.total_units) ctas = p.total_units;
+  const bool fused = p.num_splits > 1 && decode_fused_reduce();
+  if (p.num_splits > 1 && !fused) p.tickets = nullptr;
+  // one unit per CTA: nothing to balance, skip the counter round trips
+  if (!fused && p.total_units <= ctas && getenv("MVB200_DECODE_DYNAMIC") == nullptr) p.sched = nullptr;
+  cudaError_t le = launch_pdl(kern, dim3((unsigned)ctas), dim3(kDecodeThreads), (size_t)smem, stream, mk, mv, p);
   if (le != cudaSuccess)
     return fail(MVB200_ECUDA, "paged_decode_kernel: %s", cudaGetErrorString(le));
   rc = check_launch("paged_decode_kernel");
-  if (rc) return rc;
-  if (p.num_splits > 1) {
-    dim3 rgrid(p.num_heads, batch);
-    le = launch_pdl(decode_reduce_kernel<T>, rgrid, dim3(128), 0, stream, (const float*)p.part_o,
-                    (const float*)p.part_lse, (T*)p.out, p.out_row_stride, p.num_heads, D,
-                    p.num_splits);
-    if (le != cudaSuccess)
-      return fail(MVB200_ECUDA, "decode_reduce_kernel: %s", cudaGetErrorString(le));
-    rc = check_launch("decode_reduce_kernel");
-  }
-  return rc;
+  if (rc || p.num_splits == 1 || fused) return rc;
+  dim3 rgrid(p.num_heads, p.batch);
+  le = launch_pdl(decode_reduce_kernel<T>, rgrid, dim3(128), 0, stream, (const float*)p.part_o,
+                  (const float*)p.part_lse, (T*)p.out, p.out_row_stride, p.num_heads, D, p.num_splits);
+  if (le != cudaSuccess) return fail(MVB200_ECUDA, "decode_reduce_kernel: %s", cudaGetErrorString(le));
+  return check_launch("decode_reduce_kernel");
 }
 
 template <typename T>
@@ -534,10 +774,28 @@ static int decode_stages() {
 
 }  // namespace mvb200
 
-extern "C" size_t mvb200_decode_workspace_bytes(int32_t batch, int32_t num_heads,
-                                                int32_t head_dim, int32_t num_splits) {
+static size_t decode_partial_bytes(int32_t batch, int32_t num_heads, int32_t head_dim, int32_t num_splits) {
   if (num_splits <= 1 || batch <= 0) return 0;
   return (size_t)batch * num_heads * num_splits * ((size_t)head_dim + 1) * sizeof(float);
+}
+
+extern "C" size_t mvb200_decode_workspace_bytes(int32_t batch, int32_t num_heads,
+                                                int32_t head_dim, int32_t num_splits) {
+  if (batch <= 0) return 0;
+  return decode_partial_bytes(batch, num_heads, head_dim, num_splits) + mvb200::kDecodeTailBytes;
+}
+
+extern "C" int mvb200_decode_workspace_init(void* workspace, size_t workspace_bytes, void* stream) {
+  using namespace mvb200;
+  if (!workspace || workspace_bytes < kDecodeTailBytes || ((uintptr_t)workspace & 15) || (workspace_bytes & 15))
+    return fail(MVB200_EINVAL, "decode_workspace_init: need a 16-byte aligned buffer of at least %zu bytes "
+                               "(a multiple of 16)", kDecodeTailBytes);
+  cudaStream_t s = (cudaStream_t)stream;
+  char* tail = (char*)workspace + workspace_bytes - kDecodeTailBytes;
+  cudaError_t e = cudaMemsetAsync(tail, 0, kDecodeTailBytes, s);
+  if (e != cudaSuccess) return fail(MVB200_ECUDA, "decode_workspace_init: %s", cudaGetErrorString(e));
+  decode_workspace_init_kernel<<<1, 1, 0, s>>>((uint32_t*)(tail + (size_t)kDecodeMaxTickets * 4));
+  return check_launch("decode_workspace_init_kernel");
 }
 
 extern "C" int32_t mvb200_decode_suggest_splits(int32_t batch, int32_t num_kv_heads,
@@ -546,14 +804,20 @@ extern "C" int32_t mvb200_decode_suggest_splits(int32_t batch, int32_t num_kv_he
   if (sm_count <= 0) sm_count = 148;
   const int64_t units = (int64_t)batch * num_kv_heads;
   const int tiles = max_context > 0 ? (max_context + 63) / 64 : 1;
-  // Plenty of (sequence, kv head) units: two waves of two resident CTAs per SM.  Fewer units than SMs
-  // (long-context, small-batch decode): one CTA per SM in a single wave — measured on B200 at
-  // 1 x 32k x 4 kv heads: 128 CTAs 21 us, 296 CTAs 27 us, 512 CTAs 36 us (per-CTA prologue and the
-  // split reduction grow with the split count).
-  const int64_t want = units >= sm_count ? 4LL * sm_count : (int64_t)sm_count;
-  int64_t s = units >= sm_count ? (want + units - 1) / units : want / units;
-  const int max_by_work = tiles / 4 > 0 ? tiles / 4 : 1;  // keep >= 4 tiles (128 KiB) per CTA
+  // The kernel is persistent (two resident CTAs per SM walk the (sequence, split, kv head) units, drawing
+  // them from a device-side counter), so plenty of units need no split at all.  Fewer units than resident
+  // CTAs: split until every CTA slot has a unit, keeping >= 4 tiles (128 KiB of K+V) per unit.
+  // Measured on B200 (profiles/r02_decode_sweep_*): 256 units (one TP8 rank of cfg2) 44 us unsplit vs 48-51 us
+  // with 2-4 splits; 4 units (1 x 32k) 21-22 us at 37-74 splits vs 28 us at 18.
+  const int64_t slots = 2LL * sm_count;
+  int64_t s = units >= sm_count ? 1 : (slots + units - 1) / units;
+  static const int env_cap = [] {
+    const char* e = getenv("MVB200_DECODE_MAX_SPLITS");
+    return e ? atoi(e) : 0;
+  }();
+  const int max_by_work = tiles / 4 > 0 ? tiles / 4 : 1;
   if (s > max_by_work) s = max_by_work;
+  if (env_cap > 0 && s > env_cap) s = env_cap;
   if (s < 1) s = 1;
   if (s > 128) s = 128;
   return (int32_t)s;
@@ -595,8 +859,7 @@ extern "C" int mvb200_paged_decode(const void* q, int64_t q_row_stride, const vo
   const bool fast = eb == 2 && (head_dim == 64 || head_dim == 128) && block_size % 64 == 0 &&
                     group <= 16 && num_blocks < (1LL << 31) &&
                     ((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) &&
-                    ((uintptr_t)q % 4 == 0) && (q_row_stride % 2 == 0) && batch <= 65535 &&
-                    num_splits <= 65535;
+                    ((uintptr_t)q % 4 == 0) && (q_row_stride % 2 == 0);
   if (fast) {
     DecodeParams p;
     p.q = q;
@@ -617,21 +880,38 @@ extern "C" int mvb200_paged_decode(const void* q, int64_t q_row_stride, const vo
     p.scale_log2 = scale * kLog2e;
     p.part_o = nullptr;
     p.part_lse = nullptr;
+    p.tickets = nullptr;
+    p.sched = nullptr;
+    p.batch = batch;
+    const int64_t units = (int64_t)batch * num_kv_heads;
+    // Without an (initialised) workspace, or beyond the ticket capacity, the kernel still works: no
+    // splits, units dealt round-robin instead of drawn from the device-side counter.
+    const bool have_tail = workspace && workspace_bytes >= kDecodeTailBytes && units <= kDecodeMaxTickets &&
+                           ((uintptr_t)workspace & 15) == 0 && (workspace_bytes & 15) == 0;
     if (num_splits > 1) {
       const size_t need = mvb200_decode_workspace_bytes(batch, num_heads, head_dim, num_splits);
-      if (!workspace || workspace_bytes < need)
-        return fail(MVB200_EINVAL, "paged_decode: workspace %zu B < %zu B needed for %d splits",
-                    workspace_bytes, need, num_splits);
+      if (!have_tail || workspace_bytes < need)
+        return fail(MVB200_EINVAL, "paged_decode: workspace %zu B < %zu B needed for %d splits (or batch * "
+                                   "kv heads > %d, or buffer not 16-byte aligned)",
+                    workspace_bytes, need, num_splits, kDecodeMaxTickets);
       p.part_o = (float*)workspace;
       p.part_lse = p.part_o + (size_t)batch * num_heads * num_splits * head_dim;
     }
-    note_kernel("decode_tma_mma");
-    if (dtype == MVB200_BF16) {
-      return head_dim == 128 ? launch_fast<__nv_bfloat16, 128>(p, k_cache, v_cache, block_size, batch, s)
-                             : launch_fast<__nv_bfloat16, 64>(p, k_cache, v_cache, block_size, batch, s);
+    if (have_tail) {
+      char* tail = (char*)workspace + workspace_bytes - kDecodeTailBytes;
+      p.tickets = (int32_t*)tail;
+      p.sched = (int32_t*)(tail + (size_t)kDecodeMaxTickets * 4);
     }
-    return head_dim == 128 ? launch_fast<__half, 128>(p, k_cache, v_cache, block_size, batch, s)
-                           : launch_fast<__half, 64>(p, k_cache, v_cache, block_size, batch, s);
+    if (units * num_splits >= (1LL << 31)) return fail(MVB200_EINVAL, "paged_decode: too many work units");
+    p.total_units = (int32_t)(units * num_splits);
+    p.q_bulk = (((uintptr_t)q & 15) == 0 && (q_row_stride % 8) == 0) ? 1 : 0;
+    note_kernel(num_splits > 1 ? "decode_tma_mma_fused_reduce" : "decode_tma_mma");
+    if (dtype == MVB200_BF16) {
+      return head_dim == 128 ? launch_fast<__nv_bfloat16, 128>(p, k_cache, v_cache, block_size, s)
+                             : launch_fast<__nv_bfloat16, 64>(p, k_cache, v_cache, block_size, s);
+    }
+    return head_dim == 128 ? launch_fast<__half, 128>(p, k_cache, v_cache, block_size, s)
+                           : launch_fast<__half, 64>(p, k_cache, v_cache, block_size, s);
   }
   if (head_dim > 256)
     return fail(MVB200_EUNSUPPORTED, "paged_decode: head_dim %d > 256", head_dim);

@@ -265,7 +265,7 @@ class HotPathExecutor:
             "context_lens": torch.zeros(max_bs, dtype=torch.int32, device=dev),
             "block_tables": torch.zeros(max_bs, mb, dtype=torch.int32, device=dev),
             "outputs": torch.zeros(max_bs, self.hidden_size, dtype=self.dtype, device=dev),
-            "workspace": torch.empty(max(ws, 1), dtype=torch.float32, device=dev),
+            "workspace": ops.decode_workspace(ws, dev),  # tickets / work counter zeroed once, self re-arming
             "next_tokens": torch.zeros(max_bs, dtype=torch.int64, device=dev),
             "appends": torch.full((max_bs,), -1, dtype=torch.int32, device=dev),
         }

@@ -214,8 +214,33 @@ def decode_num_splits(batch: int, num_kv_heads: int, max_context: int, device: t
 
 
 def decode_workspace_numel(batch: int, num_heads: int, head_dim: int, num_splits: int) -> int:
-    """float32 elements of split workspace (0 when ``num_splits == 1``)."""
-    return int(_native.lib().mvb200_decode_workspace_bytes(batch, num_heads, head_dim, num_splits)) // 4
+    """float32 elements of decode workspace: split partials (when ``num_splits > 1``) plus the fixed tail
+    that holds the arrival tickets and the work counter of the persistent kernel."""
+    return (int(_native.lib().mvb200_decode_workspace_bytes(batch, num_heads, head_dim, num_splits)) + 3) // 4
+
+
+def decode_workspace(numel: int, device: torch.device) -> torch.Tensor:
+    """Allocate AND initialise a decode workspace of ``numel`` float32 (``mvb200_decode_workspace_init``:
+    tickets and counters zeroed, buffer stamped).  The kernel re-arms it after every launch, so one buffer
+    serves any number of later calls — on ONE stream at a time."""
+    numel = (max(int(numel), decode_workspace_numel(1, 1, 64, 1)) + 3) // 4 * 4
+    ws = torch.empty(numel, dtype=torch.float32, device=device)
+    rc = _native.lib().mvb200_decode_workspace_init(ws.data_ptr(), ws.numel() * 4, _stream())
+    _native.check(rc, "mvb200_decode_workspace_init")
+    return ws
+
+
+_DEFAULT_WS: dict[tuple[int, int], torch.Tensor] = {}
+
+
+def _default_decode_workspace(need: int, device: torch.device) -> torch.Tensor:
+    """Per (device, stream) workspace for eager calls that pass none (grown on demand)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), _stream())
+    ws = _DEFAULT_WS.get(key)
+    if ws is None or ws.numel() < need:
+        ws = decode_workspace(max(need, 1 << 20), device)
+        _DEFAULT_WS[key] = ws
+    return ws
 
 
 def paged_decode_attention(
@@ -272,13 +297,19 @@ def paged_decode_attention(
     if num_splits is None:
         num_splits = decode_num_splits(b, kvh, mb * bs, q.device) if mb > 0 else 1
     ws_ptr, ws_bytes = 0, 0
-    if num_splits > 1 and mb > 0:
+    if mb > 0:
         need = decode_workspace_numel(b, h, d, num_splits)
         if workspace is None:
-            workspace = torch.empty(need, dtype=torch.float32, device=q.device)
+            if torch.cuda.is_current_stream_capturing():
+                # a captured launch cannot share the eager default workspace (its lifetime is not the
+                # graph's): without one, capture the split-free, statically scheduled variant
+                num_splits = 1
+            else:
+                workspace = _default_decode_workspace(need, q.device)
         elif workspace.numel() * workspace.element_size() < need * 4 or not workspace.is_contiguous():
-            raise ValueError(f"decode workspace too small: need {need} float32")
-        ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+            raise ValueError(f"decode workspace too small: need {need} float32 (ops.decode_workspace)")
+        if workspace is not None:
+            ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
     rc = _native.lib().mvb200_paged_decode(
         q.data_ptr(), _row_stride(q), k_cache.data_ptr(), v_cache.data_ptr(),
         block_tables.data_ptr() if mb > 0 else 0, block_tables.stride(0) if mb > 0 else 0,

@@ -12,6 +12,8 @@ and ``Context`` accessors.
 | ``_prepare_decode_input`` + ``_prepare_block_tables_decode`` (:551-688) | ``HotPathExecutor.prepare_decode`` | per-sequence ``torch.tensor`` per step -> one vectorised fill, pinned staging |
 | ``capture_device_graphs`` (:823-920)                 | ``HotPathExecutor.capture_graphs``            | ``outputs.copy_(model(...)[0])`` row-0 broadcast, fp32 outputs buffer, frozen split count + workspace |
 | ``_execute_with_cuda_graph`` (:728-774)              | ``HotPathExecutor.replay_decode`` + ``compute_logits`` | same replay protocol on the buffers above |
+| ``_sample_tokens`` (:776-806), all-greedy batches only | ``ops.greedy_argmax``                         | the full sampling pipeline + multinomial on a one-hot distribution |
+| ``initialize`` (:184-196), ``execute_batch`` (:412-449), TP > 1 only | same + capture on every rank; workers skip logits/sampling | graphs captured on rank 0 only (model_runner.py:113-115); ``ParallelLMHead`` returns ``None`` off rank 0 |
 
 The scheduler, block manager, sequences, models, sampler and ``LLM.generate`` are untouched.
 """
@@ -137,6 +139,23 @@ def install_executor() -> None:
         with torch.inference_mode():
             return self.model.compute_logits(out)  # None on TP workers
 
+    orig_sample = cls._sample_tokens
+
+    def _sample_tokens(self, logits, sequences):
+        """Greedy fast path: when every sequence asks for ``temperature == 0`` the
+        reference still builds four per-step tensors and runs its whole temperature / top-k / top-p / min-p
+        pipeline before ``torch.multinomial`` on a one-hot distribution (inference_executor.py:776-806,
+        sampling/functional.py:434-436) — i.e. the argmax its sampler documents for this case
+        (sampler.py:104-108).  One ``greedy_argmax`` launch instead; ties go to the lowest index."""
+        if logits is None:  # TP worker: the logits live on rank 0 (embed_head.py:217-229)
+            return []
+        if logits.is_cuda and logits.dim() == 2 and all(seq.temperature == 0 for seq in sequences):
+            from . import ops
+
+            return ops.greedy_argmax(logits).tolist()
+        return orig_sample(self, logits, sequences)
+
+    cls._sample_tokens = _sample_tokens
     cls.__init__ = __init__
     cls.initialize = initialize
     cls.execute_batch = execute_batch

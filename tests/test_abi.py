@@ -37,14 +37,16 @@ def test_library_exports_every_declared_symbol(native):
     for sym in _declared_symbols():
         assert hasattr(handle, sym), f"{sym} declared in mvb200.h but not exported"
     assert sorted(native.SIGNATURES) == _declared_symbols()
-    assert native.lib().mvb200_version() == 110
+    assert native.lib().mvb200_version() == 120
 
 
 def test_host_side_helpers_need_no_gpu(native):
     lib = native.lib()
-    # workspace: B*H*S*(D+1) floats when S > 1, nothing for a single split
-    assert lib.mvb200_decode_workspace_bytes(256, 16, 128, 1) == 0
-    assert lib.mvb200_decode_workspace_bytes(256, 16, 128, 4) == 256 * 16 * 4 * 129 * 4
+    # workspace: B*H*S*(D+1) floats of partials when S > 1, plus the fixed tail (65536 tickets + 16 counters)
+    tail = 65536 * 4 + 64
+    assert lib.mvb200_decode_workspace_bytes(256, 16, 128, 1) == tail
+    assert lib.mvb200_decode_workspace_bytes(256, 16, 128, 4) == 256 * 16 * 4 * 129 * 4 + tail
+    assert lib.mvb200_decode_workspace_init(None, 0, None) == 1  # EINVAL without touching a GPU
     # plenty of (sequence, kv head) units -> no split; one long sequence -> many splits
     assert lib.mvb200_decode_suggest_splits(256, 8, 2048, 148) == 1
     s = lib.mvb200_decode_suggest_splits(1, 4, 32768, 148)
