@@ -346,7 +346,11 @@ class HotPathExecutor:
         gv["next_tokens"][:bs].copy_(self._to_device(tok, torch.int64))
         gv["appends"][:bs].fill_(-1)
         self._loop_b, self._loop_bs = b, bs
-        self._h_app = self._host(bs, torch.int32)
+        # two pinned staging buffers + events: a caller that runs ahead of the device (pipelined sampling) must not
+        # rewrite a buffer whose H2D copy has not executed yet
+        self._h_app = [self._host(bs, torch.int32), self._host(bs, torch.int32)]
+        self._h_app_done = [None, None]
+        self._h_app_turn = 0
         return bs
 
     @torch.inference_mode()
@@ -360,11 +364,20 @@ class HotPathExecutor:
             raise RuntimeError("step_decode called before begin_decode")
         gv = self.graph_vars
         if appends:
-            self._h_app.fill_(-1)
-            view = self._h_app.numpy()
+            i = self._h_app_turn
+            self._h_app_turn ^= 1
+            if self._h_app_done[i] is not None:
+                self._h_app_done[i].synchronize()  # the copy issued two uploads ago has read this buffer
+            buf = self._h_app[i]
+            buf.fill_(-1)
+            view = buf.numpy()
             for row, block in appends.items():
                 view[row] = block
-            gv["appends"][:bs].copy_(self._h_app, non_blocking=True)
+            gv["appends"][:bs].copy_(buf, non_blocking=True)
+            if buf.is_pinned():
+                ev = self._h_app_done[i] or torch.cuda.Event()
+                ev.record()
+                self._h_app_done[i] = ev
         if bs in self.graphs:
             self.graphs[bs].replay()
         else:  # eager twin (enforce_eager)

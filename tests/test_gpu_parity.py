@@ -556,6 +556,34 @@ def test_prefill_tcgen05_dense_strided_source(m, cuda_device):
     assert np.abs(_f32(out) - ref).max() <= TOL["bf16"]
 
 
+@pytest.mark.parametrize("dtype,d", [("bf16", 128), ("f16", 128), ("bf16", 64), ("f32", 128)])
+def test_prefill_fewer_keys_than_queries(m, cuda_device, dtype, d):
+    """Lk < Lq (bottom-right causal mask, attention.py:584-587): the first Lq - Lk query rows see no key at all and
+    must come out as zeros (documented deviation: torch gives NaN there), the others match the oracle.  The rows
+    without keys sit in tiles that do have keys, i.e. they run through the softmax (FMA-pipe exponentials included)."""
+    h, kvh = 4, 2
+    lq = [300, 70, 129, 5]
+    lk = [200, 69, 1, 5]
+    g = torch.Generator().manual_seed(8)
+    q = torch.randn(sum(lq), h, d, generator=g).to(TDT[dtype]).to(cuda_device)
+    k = torch.randn(sum(lk), kvh, d, generator=g).to(TDT[dtype]).to(cuda_device)
+    v = torch.randn(sum(lk), kvh, d, generator=g).to(TDT[dtype]).to(cuda_device)
+    cu_q = np.concatenate([[0], np.cumsum(lq)]).astype(np.int32)
+    cu_k = np.concatenate([[0], np.cumsum(lk)]).astype(np.int32)
+    out = _f32(m.prefill_varlen_attention(q, k, v, torch.from_numpy(cu_q).to(cuda_device), torch.from_numpy(cu_k).to(cuda_device),
+                                          max(lq), max(lk), d**-0.5))
+    if dtype != "f32" and d == 128:
+        assert m.ops.last_kernel().startswith("prefill_tcgen05")
+    with np.errstate(invalid="ignore"):
+        ref = orc.prefill_dense(_f32(q), _f32(k), _f32(v), cu_q, cu_k, d**-0.5)
+    for s in range(len(lq)):
+        blind = max(0, lq[s] - lk[s])
+        a = int(cu_q[s])
+        assert (out[a : a + blind] == 0).all(), (s, np.abs(out[a : a + blind]).max())
+        err = np.abs(out[a + blind : a + lq[s]] - ref[a + blind : a + lq[s]])
+        assert np.isfinite(out[a : a + lq[s]]).all() and (err.size == 0 or err.max() <= TOL[dtype]), (s, err.max())
+
+
 @pytest.mark.parametrize(
     "name,lens,cached,h,kvh",
     [
