@@ -13,8 +13,16 @@
 //   * two 128-row query tiles share every K/V tile (half the L2->smem traffic per FLOP) and
 //     ping-pong on the tensor pipe: while softmax warpgroup 0 works on S0 the pipe runs
 //     P1 V and Q1 K^T, and vice versa.
-// Roles (320 threads): warp 0 TMA producer, warp 1 MMA issuer (both warp-uniform loops, one elected
-// lane issues), warps 2-5 softmax warpgroup of query tile 0, warps 6-9 of query tile 1 (thread = row).
+// Roles: warp 0 TMA producer, warp 1 MMA issuer (both warp-uniform loops, one elected lane issues),
+// warps 2-3 idle (they keep the softmax warps on warp % 4 = TMEM lane quarter), then kHalves softmax
+// warpgroups per query tile (thread = query row x a 128/kHalves-column slice of the score tile).
+//   kHalves = 1 (384 threads): warps 4-7 tile 0, warps 8-11 tile 1, 128 scores per thread.
+//   kHalves = 2 (640 threads): warps 4-7 / 8-11 the two column halves of tile 0, 12-15 / 16-19 of tile 1.
+//     The softmax of a tile sits on the critical path  S(j) -> softmax -> P(j) V -> S(j+1)  (P aliases S in
+//     TMEM) and a lone warp per SM sub-partition issues at ~0.4 IPC (profiles/r01_prefill_v2a_trace_emu32.log:
+//     2100 of a 3500-clock period); two warps per sub-partition on the same tile interleave their MUFU and
+//     FMA work.  The halves exchange their row maxima through shared memory (named barrier of the two warps
+//     that share 32 rows) and keep separate row sums, added in the epilogue.
 // TMEM (512 columns): S0 [0,128) S1 [128,256) O0 [256,384) O1 [384,512); bf16 P overwrites S in place.
 // Tensor-bound: 4*D flops per unmasked (q,k) pair per head.
 #include <math.h>
@@ -59,7 +67,7 @@ constexpr int kQTiles = 2;               // query tiles per work item
 constexpr int kBN = 128;                 // keys per K/V tile
 constexpr int kPage = 64;                // keys per TMA box (= kvcache_block_size granularity)
 constexpr int kStages = 2;               // K ring depth = V ring depth
-constexpr int kThreads = 384;
+constexpr int kDefaultHalves = 2;        // softmax warpgroups per query tile
 constexpr int kMaxPChunks = 4;            // P is handed to the MMA warp in kPC (1, 2 or 4) column chunks per tile
 constexpr int kTileHalfBytes = 128 * 128;  // [128 rows][128 B] = one 64-column half of a tile
 constexpr int kTileBytes = 2 * kTileHalfBytes;
@@ -97,6 +105,7 @@ struct Params {
   int32_t num_blocks;
   int32_t paged;
   int32_t levels;           // ceil(max_seqlen_q / 256)
+  int32_t max_seqlen_q;
   float scale_log2;
 };
 
@@ -104,6 +113,7 @@ struct Params {
 struct Item {
   int seq, head, kvh;
   int q0, k0, lk;      // first packed query / key row of the sequence, key count
+  int lq;              // query rows of the sequence
   int shift;           // query row i sees keys 0..shift+i
   int row0[kQTiles];   // first query row of tile t within the sequence
   int rows[kQTiles];   // valid rows of tile t (0: tile absent)
@@ -127,6 +137,7 @@ MVB_DEV Item decode_item(const Params& p, int w) {
   const int lq = __ldg(p.cu_q + it.seq + 1) - it.q0;
   it.k0 = __ldg(p.cu_k + it.seq);
   it.lk = __ldg(p.cu_k + it.seq + 1) - it.k0;
+  it.lq = lq;
   it.shift = it.lk - lq;
   it.n_kt = 0;
 #pragma unroll
@@ -141,8 +152,16 @@ MVB_DEV Item decode_item(const Params& p, int w) {
   return it;
 }
 
-template <typename T, int kEmu, int kPC>
-__global__ void __launch_bounds__(kThreads, 1)
+MVB_DEV void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+template <int kRegs>
+MVB_DEV void setmaxnreg_inc() { asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegs)); }
+template <int kRegs>
+MVB_DEV void setmaxnreg_dec() { asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegs)); }
+
+template <typename T, int kEmu, int kPC, int kHalves>
+__global__ void __launch_bounds__(128 + 256 * kHalves, 1)
 prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
                     const __grid_constant__ CUtensorMap tmap_k,
                     const __grid_constant__ CUtensorMap tmap_v, const Params p) {
@@ -155,7 +174,11 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   const uint32_t sV = sK + kStages * kTileBytes;
   const uint32_t bars = sV + kStages * kTileBytes;
   const uint32_t tmem_slot = bars + 8 * BAR_COUNT;
+  // row maxima [parity][tile][half][row] and row sums [tile][half][row] the column halves exchange
+  float* xmax = reinterpret_cast<float*>(smem_gen + (tmem_slot + 16 - smem_base));
+  float* xsum = xmax + 2 * kQTiles * 2 * kBM;
   auto bar = [&](int i) { return bars + 8u * i; };
+  static_assert(kHalves == 1 || (kHalves == 2 && kPC == 1), "column halves hand P over in one piece");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_items = p.levels * p.num_seqs * p.num_heads;
@@ -166,7 +189,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   }
   if (threadIdx.x == 32) {
     for (int i = 0; i < BAR_COUNT; ++i) {
-      mbar_init(bar(i), i >= BAR_P_FULL ? 4 : 1);
+      mbar_init(bar(i), i >= BAR_P_FULL ? 4 * kHalves : 1);
     }
     fence_mbar_init();
   }
@@ -174,6 +197,10 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+  if constexpr (kHalves == 2) {
+    // 640 threads start with 96 registers each (61440 of 65536): the softmax warpgroups take the rest
+    if (warp >= 4) setmaxnreg_inc<104>();
+  }
 
   if (warp == 0) {
     // =========================== TMA producer ===========================
@@ -187,6 +214,12 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
     uint32_t kv_cnt = 0;                // K/V tiles issued so far (stage = cnt % kStages)
     for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
       const Item it = decode_item(p, w);
+      if (it.lq > p.levels * kQTiles * kBM) {
+        // the caller's max_seqlen_q understates a sequence: its tail rows would silently stay unwritten
+        if (lane == 0) printf("mvb200: prefill: max_seqlen_q %d < query length %d of sequence %d\n",
+                              p.max_seqlen_q, it.lq, it.seq);
+        __trap();
+      }
       if (!it.valid || it.n_kt == 0) continue;
 #pragma unroll
       for (int t = 0; t < kQTiles; ++t) {
@@ -377,13 +410,19 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   } else if (warp < 4) {
     // idle warps: keep the softmax warpgroups aligned to TMEM lane quarters (warp % 4)
   } else {
-    // =========================== softmax warpgroups (thread = query row) ===========================
-    const int t = (warp - 4) >> 2;                // query tile of this warpgroup
+    // =========================== softmax warpgroups (thread = query row x column slice) ===========================
+    constexpr int kCols = kBN / kHalves;   // score columns of a row this thread owns
+    constexpr int kOCols = kD / kHalves;   // O columns this thread rescales / writes out
+    const int sw = warp - 4;
+    const int t = sw / (4 * kHalves);             // query tile of this warpgroup
+    const int half = (sw >> 2) % kHalves;         // column slice
     const int quarter = warp & 3;                 // TMEM lanes this warp may touch
     const int r = quarter * 32 + lane;            // query row within the tile
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
-    const uint32_t s_col = lane_base + kColS + t * kBN;
-    const uint32_t o_col = lane_base + kColO + t * kD;
+    const uint32_t s_col = lane_base + kColS + t * kBN + half * kCols;
+    const uint32_t p_col = lane_base + kColS + t * kBN + half * (kCols / 2);  // bf16 pairs: half the columns
+    const uint32_t o_col = lane_base + kColO + t * kD + half * kOCols;
+    const int pair_bar = 1 + t * 4 + quarter;     // named barrier of the two warps that own the same 32 rows
     T* out = reinterpret_cast<T*>(p.out);
     uint32_t c = 0;        // S tiles consumed by this warpgroup so far (= P V commits it may wait for)
     uint32_t kv_cnt = 0;   // K/V tiles streamed by the CTA before the current item
@@ -399,50 +438,60 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
       const int kv_end_t = t ? it.kv_end[1] : it.kv_end[0];
       const int n_t = t ? it.n[1] : it.n[0];
       if (rows_t == 0) continue;
-      T* orow = out + (int64_t)(it.q0 + row0_t + r) * p.out_row_stride + (int64_t)it.head * kD;
+      T* orow = out + (int64_t)(it.q0 + row0_t + r) * p.out_row_stride + (int64_t)it.head * kD + half * kOCols;
       if (n_t == 0) {  // Lk < Lq corner: rows that see no key produce zeros
         if (r < rows_t)
 #pragma unroll
-          for (int i = 0; i < kD; i += 8) *reinterpret_cast<uint4*>(orow + i) = make_uint4(0, 0, 0, 0);
+          for (int i = 0; i < kOCols; i += 8) *reinterpret_cast<uint4*>(orow + i) = make_uint4(0, 0, 0, 0);
         continue;
       }
 #ifdef PF_TRACE
-      const bool traced = blockIdx.x == 0 && w == (int)blockIdx.x + (int)gridDim.x && lane == 0 && quarter == 0;
+      const bool traced = blockIdx.x == 0 && w == (int)blockIdx.x + (int)gridDim.x && lane == 0 && quarter == 0 && half == 0;
 #endif
       const int q_limit = it.shift + row0_t + r;  // largest key index this row may see
-      float m_ref = -INFINITY, l_run = 0.f;
+      float m_ref = -INFINITY, l_run = 0.f;       // l_run: this thread's columns only
 
       for (int j = 0; j < n_t; ++j, ++c) {
         PF2_T(2 + t, j, 0);
         mbar_wait(bar(BAR_S_FULL + t), c & 1);
         PF2_T(2 + t, j, 1);
         tc_fence_after();
-        float s[kBN];
+        float s[kCols];
         {
-          uint32_t raw[4][32];
+          uint32_t raw[kCols / 32][32];
 #pragma unroll
-          for (int g = 0; g < 4; ++g) tmem_ld32(s_col + 32 * g, raw[g]);
+          for (int g = 0; g < kCols / 32; ++g) tmem_ld32(s_col + 32 * g, raw[g]);
           tmem_wait_ld();
           PF2_T(2 + t, j, 2);
 #pragma unroll
-          for (int g = 0; g < 4; ++g)
+          for (int g = 0; g < kCols / 32; ++g)
 #pragma unroll
             for (int i = 0; i < 32; ++i) s[32 * g + i] = __uint_as_float(raw[g][i]);
         }
         const int col0 = j * kBN;
         if (col0 + kBN - 1 > it.shift + row0_t) {  // tile touches the diagonal / the end (uniform test)
-          const int lim = q_limit - col0;
+          const int lim = q_limit - col0 - half * kCols;
 #pragma unroll
-          for (int i = 0; i < kBN; ++i) s[i] = i <= lim ? s[i] : -INFINITY;
+          for (int i = 0; i < kCols; ++i) s[i] = i <= lim ? s[i] : -INFINITY;
         }
         float mx4[4];  // four independent chains of 3-input max (a single chain is 64 dependent ops)
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4) {
-          mx4[q4] = fmaxf(s[32 * q4], s[32 * q4 + 1]);
+          constexpr int kQ = kCols / 4;
+          mx4[q4] = fmaxf(s[kQ * q4], s[kQ * q4 + 1]);
 #pragma unroll
-          for (int i = 2; i < 32; i += 2) mx4[q4] = fmaxf(mx4[q4], fmaxf(s[32 * q4 + i], s[32 * q4 + i + 1]));
+          for (int i = 2; i < kQ; i += 2) mx4[q4] = fmaxf(mx4[q4], fmaxf(s[kQ * q4 + i], s[kQ * q4 + i + 1]));
         }
-        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
+        float mxl = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        if constexpr (kHalves == 2) {
+          // row maximum over both column halves.  Slots alternate with the tile parity: the partner reads
+          // tile j's slot after barrier j and cannot be behind barrier j+1 when tile j+2 rewrites it.
+          float* slot = xmax + ((c & 1) * kQTiles + t) * 2 * kBM;
+          slot[half * kBM + r] = mxl;
+          named_bar_sync(pair_bar, 64);  // also orders the partner's tcgen05.ld of S before our P stores below
+          mxl = fmaxf(mxl, slot[(half ^ 1) * kBM + r]);
+        }
+        const float mx = mxl * p.scale_log2;
         // lazy rescale: keep exponentiating against m_ref until the true max outruns it by 2^8
         const bool grow = mx > m_ref + kRescaleThreshold;
         if (__any_sync(0xffffffffu, grow)) {
@@ -453,7 +502,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
             mbar_wait(bar(BAR_O_DONE + t), (c - 1) & 1);  // P V of the previous tile retired: O is quiescent
             tc_fence_after();
 #pragma unroll
-            for (int g = 0; g < kD; g += 16) {  // 16-column chunks: s[128] is live, registers are tight
+            for (int g = 0; g < kOCols; g += 16) {  // 16-column chunks: s[] is live, registers are tight
               uint32_t o[16];
               tmem_ld16(o_col + g, o);
               tmem_wait_ld();
@@ -464,7 +513,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
           }
           m_ref = m_new;
         }
-        if (j == n_t - 1 && quarter == 0) {
+        if (j == n_t - 1 && quarter == 0 && half == 0) {
           // keys >= Lk in the last block were never written: their V rows may hold NaN/Inf bit patterns and
           // 0 * NaN would poison O.  Zero those inside the last 16-key group the MMA reads (whole groups
           // past it are skipped by the issuer).
@@ -488,7 +537,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
         const uint64_t negm2 = pack2(-m_use, -m_use);
         uint64_t sum2[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};  // two chains: FADD2 latency off the critical path
 #pragma unroll
-        for (int chunk = 0; chunk < 4; ++chunk) {
+        for (int chunk = 0; chunk < kCols / 32; ++chunk) {
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
@@ -507,12 +556,13 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
             sum2[(i >> 1) & 1] = add2(sum2[(i >> 1) & 1], pack2(p0, p1));
             pk[i / 2] = Mma16816<T>::pack(p0, p1);
           }
-          tmem_st16(s_col + chunk * 16, pk);  // bf16 P overwrites the first 64 columns of S_t
-          if ((chunk + 1) % (4 / kPC) == 0) {  // hand this part of P to the MMA warp
+          tmem_st16(p_col + chunk * 16, pk);  // bf16 P overwrites the first 64 columns of S_t
+          constexpr int kChunksPerPiece = (kCols / 32) / kPC;
+          if ((chunk + 1) % kChunksPerPiece == 0) {  // hand this part of P to the MMA warp
             tmem_wait_st();
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar(BAR_P_FULL + t * kMaxPChunks + chunk / (4 / kPC)));
+            if (lane == 0) mbar_arrive(bar(BAR_P_FULL + t * kMaxPChunks + chunk / kChunksPerPiece));
           }
         }
         float sum_lo, sum_hi;
@@ -524,11 +574,19 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
       }
 
       // ---- epilogue: O / l -> global ----
+      float l_tot = l_run;
+      if constexpr (kHalves == 2) {
+        // (the next write of this slot is an item later, behind at least one pair barrier of that item)
+        xsum[(t * 2 + half) * kBM + r] = l_run;
+        named_bar_sync(pair_bar, 64);
+        l_tot += xsum[(t * 2 + (half ^ 1)) * kBM + r];
+      }
       mbar_wait(bar(BAR_O_DONE + t), (c - 1) & 1);
       tc_fence_after();
-      const float inv = l_run > 0.f ? 1.f / l_run : 0.f;
+      // a row that sees no key (Lk < Lq) still sums 2^-126 per FMA-pipe exponential: it must produce zeros
+      const float inv = (l_tot > 0.f && q_limit >= 0) ? 1.f / l_tot : 0.f;
 #pragma unroll
-      for (int g = 0; g < kD; g += 32) {
+      for (int g = 0; g < kOCols; g += 32) {
         uint32_t o[32];
         tmem_ld32(o_col + g, o);
         tmem_wait_ld();
@@ -554,7 +612,7 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   if (warp == 0) tmem_dealloc(tmem, kTmemCols);
 }
 
-template <typename T, int kEmu, int kPC>
+template <typename T, int kEmu, int kPC, int kHalves>
 static int launch(const PrefillArgs& a, cudaStream_t stream) {
   CUtensorMap mq, mk, mv;
   {
@@ -600,10 +658,12 @@ static int launch(const PrefillArgs& a, cudaStream_t stream) {
   p.num_blocks = paged ? (int32_t)a.num_blocks : 0;
   p.paged = paged ? 1 : 0;
   p.levels = (a.max_seqlen_q + kQTiles * kBM - 1) / (kQTiles * kBM);
+  p.max_seqlen_q = a.max_seqlen_q;
   p.scale_log2 = a.scale * kLog2e;
 
-  constexpr int smem = (kQTiles + 2 * kStages) * kTileBytes + 8 * BAR_COUNT + 16 + 1024;
-  auto kern = prefill_fa2q_kernel<T, kEmu, kPC>;
+  constexpr int kThreads = 128 + 256 * kHalves;
+  constexpr int smem = (kQTiles + 2 * kStages) * kTileBytes + 8 * BAR_COUNT + 16 + 3 * kQTiles * 2 * kBM * 4 + 1024;
+  auto kern = prefill_fa2q_kernel<T, kEmu, kPC, kHalves>;
   static SmemOptIn optin;
   if (int rc = optin_dynamic_smem((const void*)kern, smem, &optin, "prefill_fa2q")) return rc;
   const int num_sms = device_sm_count();
@@ -640,24 +700,35 @@ int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream) {
   static const int emu = [] {
     const char* e = getenv("MVB200_PREFILL_EMU");
     const int v = e ? atoi(e) : fa2q::kDefaultEmu;
-    return (v == 0 || v == 16 || v == 32 || v == 48) ? v : fa2q::kDefaultEmu;
+    return (v == 0 || v == 16 || v == 32 || v == 48 || v == 64) ? v : fa2q::kDefaultEmu;
   }();
   static const int pchunks = [] {
     const char* e = getenv("MVB200_PREFILL_PCHUNKS");
     const int v = e ? atoi(e) : fa2q::kDefaultPChunks;
     return (v == 1 || v == 2 || v == 4) ? v : fa2q::kDefaultPChunks;
   }();
-#define MVB_FA2Q_CASE(E, C) \
-  if (emu == E && pchunks == C) return bf ? fa2q::launch<__nv_bfloat16, E, C>(a, stream) : fa2q::launch<__half, E, C>(a, stream);
+  static const int halves = [] {
+    const char* e = getenv("MVB200_PREFILL_HALVES");
+    const int v = e ? atoi(e) : fa2q::kDefaultHalves;
+    return (v == 1 || v == 2) ? v : fa2q::kDefaultHalves;
+  }();
+#define MVB_FA2Q_CASE(E, C)                                                                                   \
+  if (emu == E && pchunks == C && halves == 1)                                                                \
+    return bf ? fa2q::launch<__nv_bfloat16, E, C, 1>(a, stream) : fa2q::launch<__half, E, C, 1>(a, stream);
+#define MVB_FA2Q_CASE2(E)                                                                                     \
+  if (emu == E && halves == 2)                                                                                \
+    return bf ? fa2q::launch<__nv_bfloat16, E, 1, 2>(a, stream) : fa2q::launch<__half, E, 1, 2>(a, stream);
   MVB_FA2Q_CASE(0, 1) MVB_FA2Q_CASE(0, 2) MVB_FA2Q_CASE(0, 4)
   MVB_FA2Q_CASE(16, 1) MVB_FA2Q_CASE(16, 2) MVB_FA2Q_CASE(16, 4)
   MVB_FA2Q_CASE(32, 1) MVB_FA2Q_CASE(32, 2) MVB_FA2Q_CASE(32, 4)
   MVB_FA2Q_CASE(48, 1) MVB_FA2Q_CASE(48, 2) MVB_FA2Q_CASE(48, 4)
+  MVB_FA2Q_CASE2(0) MVB_FA2Q_CASE2(16) MVB_FA2Q_CASE2(32) MVB_FA2Q_CASE2(48) MVB_FA2Q_CASE2(64)
 #undef MVB_FA2Q_CASE
-  return fail(MVB200_EINVAL, "prefill: no kernel instance for emu %d / pchunks %d", emu, pchunks);
+#undef MVB_FA2Q_CASE2
+  return fail(MVB200_EINVAL, "prefill: no kernel instance for emu %d / pchunks %d / halves %d", emu, pchunks, halves);
 #else
-  return bf ? fa2q::launch<__nv_bfloat16, fa2q::kDefaultEmu, fa2q::kDefaultPChunks>(a, stream)
-            : fa2q::launch<__half, fa2q::kDefaultEmu, fa2q::kDefaultPChunks>(a, stream);
+  return bf ? fa2q::launch<__nv_bfloat16, fa2q::kDefaultEmu, fa2q::kDefaultPChunks, fa2q::kDefaultHalves>(a, stream)
+            : fa2q::launch<__half, fa2q::kDefaultEmu, fa2q::kDefaultPChunks, fa2q::kDefaultHalves>(a, stream);
 #endif
 }
 
