@@ -197,11 +197,10 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
-  if constexpr (kHalves == 2) {
-    // 640 threads start with 96 registers each (61440 of 65536): the softmax warpgroups take the rest
-    if (warp >= 4) setmaxnreg_inc<104>();
+  if (warp < 4) {
+    // one setmaxnreg for the whole warpgroup 0 (TMA, MMA and the two idle warps): 128 x 88 + 512 x 104 = 64512
+    if constexpr (kHalves == 2) setmaxnreg_dec<88>();
   }
-
   if (warp == 0) {
     // =========================== TMA producer ===========================
     if (elect_one()) {
@@ -411,6 +410,8 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
     // idle warps: keep the softmax warpgroups aligned to TMEM lane quarters (warp % 4)
   } else {
     // =========================== softmax warpgroups (thread = query row x column slice) ===========================
+    // 640 threads start with 96 registers each (61440 of 65536): the softmax warpgroups take the rest
+    if constexpr (kHalves == 2) setmaxnreg_inc<104>();
     constexpr int kCols = kBN / kHalves;   // score columns of a row this thread owns
     constexpr int kOCols = kD / kHalves;   // O columns this thread rescales / writes out
     const int sw = warp - 4;
