@@ -198,8 +198,8 @@ prefill_fa2q_kernel(const __grid_constant__ CUtensorMap tmap_q,
   tc_fence_after();
   const uint32_t tmem = *reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
   if (warp < 4) {
-    // one setmaxnreg for the whole warpgroup 0 (TMA, MMA and the two idle warps): 128 x 88 + 512 x 104 = 64512
-    if constexpr (kHalves == 2) setmaxnreg_dec<88>();
+    // one setmaxnreg for the whole warpgroup 0 (TMA, MMA and the two idle warps): the CTA pool is its launch allocation, 640 x 96: 128 x 64 + 512 x 104 = 61440
+    if constexpr (kHalves == 2) setmaxnreg_dec<64>();
   }
   if (warp == 0) {
     // =========================== TMA producer ===========================
