@@ -67,7 +67,7 @@ constexpr int kQTiles = 2;               // query tiles per work item
 constexpr int kBN = 128;                 // keys per K/V tile
 constexpr int kPage = 64;                // keys per TMA box (= kvcache_block_size granularity)
 constexpr int kStages = 2;               // K ring depth = V ring depth
-constexpr int kDefaultHalves = 2;        // softmax warpgroups per query tile
+constexpr int kDefaultHalves = 1;        // softmax warpgroups per query tile (2 measured slower: profiles/r02_prefill_ab_run5.jsonl)
 constexpr int kMaxPChunks = 4;            // P is handed to the MMA warp in kPC (1, 2 or 4) column chunks per tile
 constexpr int kTileHalfBytes = 128 * 128;  // [128 rows][128 B] = one 64-column half of a tile
 constexpr int kTileBytes = 2 * kTileHalfBytes;
