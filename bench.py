@@ -470,7 +470,7 @@ def run_decode(env: Env, args, wl, wl_key) -> dict:
     def decode_only():
         for l, a in enumerate(layers):
             m.paged_decode_attention(q, a.k_cache, a.v_cache, block_tables, context_lens, scale,
-                                     num_splits=splits, workspace=workspace, out=outs[l])
+                                     num_splits=splits, workspace=workspace, out=outs[l], kv_prefix_stable=True)
 
     def capture(fn):
         side = torch.cuda.Stream()

@@ -36,7 +36,7 @@ extern "C" {
 #define MVB200_API
 #endif
 
-#define MVB200_VERSION 120
+#define MVB200_VERSION 130
 
 /* element types */
 #define MVB200_F32 0
@@ -115,6 +115,25 @@ MVB200_API int mvb200_paged_decode(const void* q, int64_t q_row_stride,
                         int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
                         int32_t block_size, int64_t num_blocks, int32_t max_blocks_per_seq,
                         int32_t num_splits, float scale, int32_t dtype, void* stream);
+
+/* Flags of mvb200_paged_decode_ex. */
+/* The caller vouches that the kernel launched immediately before this one on the stream writes neither
+ * block_tables / context_lens nor any K/V row other than the NEWEST token of each sequence (position
+ * context_lens[b] - 1) — true for the layer's decode path, whose predecessor is the store_kvcache of the
+ * step's new tokens (attention.py:237-243).  Under programmatic dependent launch the kernel then starts
+ * streaming the older K/V tiles while that predecessor is still draining. */
+#define MVB200_DECODE_KV_PREFIX_STABLE 1u
+
+/* mvb200_paged_decode with flags (0 = the call above). */
+MVB200_API int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride,
+                           const void* k_cache, const void* v_cache,
+                           const int32_t* block_tables, int64_t bt_row_stride,
+                           const int32_t* context_lens,
+                           void* out, int64_t out_row_stride,
+                           void* workspace, size_t workspace_bytes,
+                           int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
+                           int32_t block_size, int64_t num_blocks, int32_t max_blocks_per_seq,
+                           int32_t num_splits, float scale, int32_t dtype, uint32_t flags, void* stream);
 
 /*
  * varlen causal prefill attention.

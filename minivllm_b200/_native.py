@@ -9,7 +9,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
+from ctypes import c_char_p, c_float, c_int32, c_int64, c_size_t, c_uint32, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # MVB200_LIB points debugging tools at an instrumented build of the same sources (tools/prefill_trace.py)
@@ -37,6 +37,13 @@ SIGNATURES = {
          c_void_p, c_int64, c_void_p, c_size_t,
          c_int32, c_int32, c_int32, c_int32, c_int32, c_int64, c_int32,
          c_int32, c_float, c_int32, c_void_p],
+    ),
+    "mvb200_paged_decode_ex": (
+        c_int32,
+        [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
+         c_void_p, c_int64, c_void_p, c_size_t,
+         c_int32, c_int32, c_int32, c_int32, c_int32, c_int64, c_int32,
+         c_int32, c_float, c_int32, c_uint32, c_void_p],
     ),
     "mvb200_prefill_varlen": (
         c_int32,

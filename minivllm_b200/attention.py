@@ -156,6 +156,9 @@ class Attention(nn.Module):
             q, k_cache, v_cache, context.block_tables, context.context_lens, self.scale,
             num_splits=getattr(context, "decode_num_splits", None),
             workspace=getattr(context, "decode_workspace", None),
+            # the launch before this one is the store of the step's new tokens (one slot per sequence, the
+            # newest position: inference_executor.py:568-572) or nothing of ours at all
+            kv_prefix_stable=True,
         )
 
 

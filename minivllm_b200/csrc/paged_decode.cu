@@ -70,6 +70,7 @@ struct DecodeParams {
   int32_t stages;
   int32_t total_units;  // B * num_splits * KVH
   int32_t q_bulk;       // Q rows of a unit can be fetched with one 16-byte-aligned bulk copy
+  int32_t early;        // MVB200_DECODE_KV_PREFIX_STABLE: K/V tiles may be fetched before the dependency wait
   float scale_log2;
 };
 
@@ -137,8 +138,15 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
     tma_prefetch_desc(&tmap_v);
   }
   __syncthreads();
-  pdl_wait();               // q, context_lens, block tables and the freshly stored K/V are visible from here
-  pdl_launch_dependents();  // the next kernel may start its own prologue
+  // q, context_lens, block tables and the freshly stored K/V are visible after the dependency wait.  With
+  // p.early the caller vouches that the kernel launched just before this one writes only the NEWEST token of
+  // each sequence (and q): the producer warp then starts streaming the older tiles of its first unit while
+  // that kernel is still draining, and waits just before the first load that could see its writes.
+  const bool run_ahead = p.early && warp == kConsumerWarps;
+  if (!run_ahead) {
+    pdl_wait();
+    pdl_launch_dependents();  // the next kernel may start its own prologue
+  }
 
   T* out = reinterpret_cast<T*>(p.out);
 
@@ -154,12 +162,19 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
       __trap();
     }
     int it = 0;
+    bool waited = !run_ahead;  // false: nothing the preceding kernel writes may be touched yet
     // The first unit is the CTA's own index (no round trip to the counter before the first load); the next
     // one is drawn when a unit STARTS, so the atomic's latency hides behind that unit's tiles.  The counter
-    // therefore counts draws beyond the first round.
+    // therefore counts draws beyond the first round.  (The preceding launch re-arms the counter as it ends:
+    // a run-ahead producer draws only after its dependency wait.)
     int u = blockIdx.x;
     for (;;) {
       if (u >= p.total_units) {
+        if (!waited) {
+          pdl_wait();
+          pdl_launch_dependents();
+          waited = true;
+        }
         if (lane == 0) {
           const int s = it % stages;
           mbar_wait(bar_base + 8 * (stages + s), ((it / stages) & 1) ^ 1);
@@ -178,7 +193,11 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
         break;
       }
       int u_next = 0;
-      if (lane == 0) u_next = p.sched != nullptr ? (int)gridDim.x + atomicAdd(p.sched, 1) : u + (int)gridDim.x;
+      bool drawn = false;
+      if (waited) {
+        if (lane == 0) u_next = p.sched != nullptr ? (int)gridDim.x + atomicAdd(p.sched, 1) : u + (int)gridDim.x;
+        drawn = true;
+      }
       const int kvh = u % KVH;
       const int rest = u / KVH;
       const int split = rest % S;
@@ -206,14 +225,34 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
         for (int i = 0; i < cnt; ++i) {
           const int bid = __shfl_sync(0xffffffffu, my_bid, i);
           const int sub = __shfl_sync(0xffffffffu, my_sub, i);
+          const int idx = base + i;  // tile of the unit
+          // Run-ahead ends before the sequence's last tile (it holds the token stored just now) and before
+          // the ring would fill up: the consumers cannot free a slot until the unit's Q — which the
+          // preceding kernels produce — has arrived on the first slot's barrier.
+          const bool end_run_ahead = !waited && (t0 + idx == n_tiles - 1 || idx == stages || idx == n - 1);
+          if (end_run_ahead && idx > 0) {
+            pdl_wait();
+            pdl_launch_dependents();
+            waited = true;
+            if (lane == 0 && p.q_bulk) {  // the Q copy the first slot's barrier is still expecting
+              const int s0 = (it - idx) % stages;
+              bulk_load_1d(q_base + s0 * kQSlotBytes,
+                           reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_row_stride + (int64_t)kvh * G * D,
+                           q_bytes, bar_base + 8 * s0);
+            }
+          } else if (end_run_ahead) {
+            pdl_wait();
+            pdl_launch_dependents();
+            waited = true;
+          }
           if (lane == 0) {
             const int s = it % stages;
             const uint32_t full = bar_base + 8 * s;
             mbar_wait(bar_base + 8 * (stages + s), ((it / stages) & 1) ^ 1);
-            const bool first = base + i == 0;
+            const bool first = idx == 0;
             if (first) uinfo[s] = UnitInfo{b, kvh, split, t0, n, ctx, {0, 0}};
             mbar_arrive_expect_tx(full, kStageBytes + (first && p.q_bulk ? q_bytes : 0u));
-            if (first && p.q_bulk)
+            if (first && p.q_bulk && waited)
               bulk_load_1d(q_base + s * kQSlotBytes,
                            reinterpret_cast<const T*>(p.q) + (int64_t)b * p.q_row_stride + (int64_t)kvh * G * D,
                            q_bytes, full);
@@ -229,6 +268,13 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
           __syncwarp();
         }
       }
+      if (!waited) {  // an empty first unit
+        pdl_wait();
+        pdl_launch_dependents();
+        waited = true;
+      }
+      if (!drawn && lane == 0)
+        u_next = p.sched != nullptr ? (int)gridDim.x + atomicAdd(p.sched, 1) : u + (int)gridDim.x;
       // the scratch slot: a ring entry without data (4 warps x G rows x D floats = 16 G D bytes never
       // exceed a stage of 256 D bytes at G <= 16)
       if (lane == 0) {
@@ -466,21 +512,25 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
 
   if (S == 1 || p.tickets == nullptr) return;  // no tickets: decode_reduce_kernel follows
   // ------------------------------ phase 2: split reduction, same kernel ------------------------------
-  // Every consumer WARP now takes (sequence, head) rows — its own index first, then from a second counter —
-  // and combines a row's S partials as soon as all splits of its (sequence, kv head) have been counted on
-  // the ticket: the units were handed out in the same order, so the wait is short, and whoever still owes
-  // a partial is running, not queued behind this CTA (a CTA gets here only after every unit was drawn).
-  // Lanes cover head_dim with 16-byte loads, eight partial rows in flight per lane; no CTA-wide barrier.
+  // The consumer warps of every CTA now take (sequence, head) rows — the CTA's own index first, then from a
+  // second counter — and combine a row's S partials as soon as all splits of its (sequence, kv head) have been
+  // counted on the ticket: the units were handed out in the same order, so the wait is short, and whoever
+  // still owes a partial is running, not queued behind this CTA (a CTA gets here only after every unit was
+  // drawn).  The four warps take interleaved splits (partial rows of different splits in flight together: a
+  // serial walk over 74 splits costs more than streaming the KV at batch 1), each against the maximum of its
+  // own splits; lanes cover head_dim with 16-byte loads.  The idle ring is the merge scratch.
   // Tickets and counters are re-armed for the next launch by their last user.
   constexpr int kVecs = D / 4;  // float4 per partial row (32 for D = 128)
   const int total_rows = p.batch * p.num_heads;
-  const int total_warps = (int)gridDim.x * kConsumerWarps;
-  int r = warp * (int)gridDim.x + blockIdx.x;  // first row: static (spread over the SMs first), later ones from the counter
+  float4* racc = reinterpret_cast<float4*>(smem_gen);                // [4 warps][32 lanes]
+  float* rml = reinterpret_cast<float*>(smem_gen + 4 * 32 * 16);     // [4] max, [4] weight sum
+  int* rnext = reinterpret_cast<int*>(smem_gen + 4 * 32 * 16 + 64);  // next row of this CTA
+  int r = blockIdx.x;
   for (;;) {
     if (r >= total_rows) {
-      if (lane == 0) {
-        const int done = atomicAdd(p.sched + 5, 1);  // every warp ends on exactly one out-of-range row
-        if (done == total_warps - 1) {
+      if (ctid == 0) {
+        const int done = atomicAdd(p.sched + 5, 1);  // every CTA ends on exactly one out-of-range row
+        if (done == (int)gridDim.x - 1) {
           p.sched[4] = 0;
           p.sched[5] = 0;
           __threadfence();
@@ -488,66 +538,73 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
       }
       break;
     }
-    int r_next = 0;
-    if (lane == 0) r_next = total_warps + atomicAdd(p.sched + 4, 1);  // latency hides behind this row
     const int b = r / p.num_heads, h = r % p.num_heads;
     int32_t* ticket = p.tickets + b * KVH + h / G;
-    if (lane == 0) {
+    if (ctid == 0) {
+      *rnext = (int)gridDim.x + atomicAdd(p.sched + 4, 1);  // latency hides behind this row
       int seen;
       do {
         asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(ticket) : "memory");
         if (seen < S) __nanosleep(32);
       } while (seen < S);
     }
-    __syncwarp();
+    consumer_sync();
     const int64_t ph = (int64_t)r * S;
-    // weights first (S <= 128: four per lane), so that the partial rows below are plain independent loads
-    float wl[4];
-    float M = -INFINITY;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int sp = lane + 32 * i;
-      wl[i] = sp < S ? __ldcg(p.part_lse + ph + sp) : -INFINITY;
-      M = fmaxf(M, wl[i]);
-    }
+    // this warp's splits: warp, warp + 4, ...  (S <= 128: at most 32 per warp, one per lane)
+    const int mine = (S - warp + kConsumerWarps - 1) / kConsumerWarps;
+    float wl = lane < mine ? __ldcg(p.part_lse + ph + warp + kConsumerWarps * lane) : -INFINITY;
+    float M = wl;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
-    float W = 0.f;
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      wl[i] = wl[i] == -INFINITY ? 0.f : exp2f(wl[i] - M);  // an empty split has weight 0 (its row holds no data)
-      W += wl[i];
-    }
-    W = warp_sum(W);
+    wl = wl == -INFINITY ? 0.f : exp2f(wl - M);  // an empty split has weight 0 (its row holds no data)
+    const float W = warp_sum(wl);
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4* rows = reinterpret_cast<const float4*>(p.part_o + ph * D) + (lane < kVecs ? lane : 0);
+    const float4* rows = reinterpret_cast<const float4*>(p.part_o + (ph + warp) * D) + (lane < kVecs ? lane : 0);
+#pragma unroll 8
+    for (int j = 0; j < mine; ++j) {
+      const float w = __shfl_sync(0xffffffffu, wl, j);
+      float4 v = __ldcg(rows + (int64_t)(kConsumerWarps * j) * kVecs);
+      if (w == 0.f) v = make_float4(0.f, 0.f, 0.f, 0.f);  // never-written row: whatever was read is dropped
+      acc.x += w * v.x;
+      acc.y += w * v.y;
+      acc.z += w * v.z;
+      acc.w += w * v.w;
+    }
+    racc[warp * 32 + lane] = acc;
+    if (lane == 0) {
+      rml[warp] = M;
+      rml[4 + warp] = W;
+    }
+    consumer_sync();
+    if (warp == 0) {
+      const float Mx = fmaxf(fmaxf(rml[0], rml[1]), fmaxf(rml[2], rml[3]));
+      float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+      float Wt = 0.f;
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int lim = min(32, S - 32 * i);
-#pragma unroll 16
-      for (int j = 0; j < lim; ++j) {
-        const float w = __shfl_sync(0xffffffffu, wl[i], j);
-        float4 v = __ldcg(rows + (int64_t)(32 * i + j) * kVecs);
-        if (w == 0.f) v = make_float4(0.f, 0.f, 0.f, 0.f);  // never-written row: whatever was read is dropped
-        acc.x += w * v.x;
-        acc.y += w * v.y;
-        acc.z += w * v.z;
-        acc.w += w * v.w;
+      for (int w4 = 0; w4 < kConsumerWarps; ++w4) {
+        const float sc = rml[w4] == -INFINITY ? 0.f : exp2f(rml[w4] - Mx);
+        const float4 a = racc[w4 * 32 + lane];
+        o.x += sc * a.x;
+        o.y += sc * a.y;
+        o.z += sc * a.z;
+        o.w += sc * a.w;
+        Wt += sc * rml[4 + w4];
+      }
+      if (lane < kVecs) {
+        const float inv = Wt > 0.f ? 1.f / Wt : 0.f;
+        T* dst = out + (int64_t)b * p.out_row_stride + (int64_t)h * D + 4 * lane;
+        dst[0] = from_f32<T>(o.x * inv);
+        dst[1] = from_f32<T>(o.y * inv);
+        dst[2] = from_f32<T>(o.z * inv);
+        dst[3] = from_f32<T>(o.w * inv);
+      }
+      if (lane == 0) {
+        const int old = atomicAdd(ticket, 1);
+        if (old == S + G - 1) *ticket = 0;  // all S splits counted and all G rows combined: re-arm
       }
     }
-    if (lane < kVecs) {
-      const float inv = W > 0.f ? 1.f / W : 0.f;
-      T* dst = out + (int64_t)b * p.out_row_stride + (int64_t)h * D + 4 * lane;
-      dst[0] = from_f32<T>(acc.x * inv);
-      dst[1] = from_f32<T>(acc.y * inv);
-      dst[2] = from_f32<T>(acc.z * inv);
-      dst[3] = from_f32<T>(acc.w * inv);
-    }
-    if (lane == 0) {
-      const int old = atomicAdd(ticket, 1);
-      if (old == S + G - 1) *ticket = 0;  // all S splits counted and all G rows combined: re-arm
-    }
-    r = __shfl_sync(0xffffffffu, r_next, 0);
+    r = *rnext;
+    consumer_sync();  // scratch and rnext are rewritten by the next row
   }
 }
 
@@ -810,7 +867,7 @@ extern "C" int32_t mvb200_decode_suggest_splits(int32_t batch, int32_t num_kv_he
   // Measured on B200 (profiles/r02_decode_sweep_*): 256 units (one TP8 rank of cfg2) 44 us unsplit vs 48-51 us
   // with 2-4 splits; 4 units (1 x 32k) 21-22 us at 37-74 splits vs 28 us at 18.
   const int64_t slots = 2LL * sm_count;
-  int64_t s = units >= sm_count ? 1 : (slots + units - 1) / units;
+  int64_t s = units >= sm_count ? 1 : slots / units;  // never more units than resident CTA slots: one wave
   static const int env_cap = [] {
     const char* e = getenv("MVB200_DECODE_MAX_SPLITS");
     return e ? atoi(e) : 0;
@@ -831,6 +888,19 @@ extern "C" int mvb200_paged_decode(const void* q, int64_t q_row_stride, const vo
                                    int32_t head_dim, int32_t block_size, int64_t num_blocks,
                                    int32_t max_blocks_per_seq, int32_t num_splits, float scale,
                                    int32_t dtype, void* stream) {
+  return mvb200_paged_decode_ex(q, q_row_stride, k_cache, v_cache, block_tables, bt_row_stride, context_lens, out,
+                                out_row_stride, workspace, workspace_bytes, batch, num_heads, num_kv_heads, head_dim,
+                                block_size, num_blocks, max_blocks_per_seq, num_splits, scale, dtype, 0u, stream);
+}
+
+extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const void* k_cache,
+                                      const void* v_cache, const int32_t* block_tables,
+                                      int64_t bt_row_stride, const int32_t* context_lens, void* out,
+                                      int64_t out_row_stride, void* workspace, size_t workspace_bytes,
+                                      int32_t batch, int32_t num_heads, int32_t num_kv_heads,
+                                      int32_t head_dim, int32_t block_size, int64_t num_blocks,
+                                      int32_t max_blocks_per_seq, int32_t num_splits, float scale,
+                                      int32_t dtype, uint32_t flags, void* stream) {
   using namespace mvb200;
   if (batch < 0 || num_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0 || block_size <= 0)
     return fail(MVB200_EINVAL, "paged_decode: bad sizes");
@@ -905,6 +975,8 @@ extern "C" int mvb200_paged_decode(const void* q, int64_t q_row_stride, const vo
     if (units * num_splits >= (1LL << 31)) return fail(MVB200_EINVAL, "paged_decode: too many work units");
     p.total_units = (int32_t)(units * num_splits);
     p.q_bulk = (((uintptr_t)q & 15) == 0 && (q_row_stride % 8) == 0) ? 1 : 0;
+    static const bool no_early = getenv("MVB200_DECODE_NO_EARLY") != nullptr;
+    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early) ? 1 : 0;
     note_kernel(num_splits > 1 ? "decode_tma_mma_fused_reduce" : "decode_tma_mma");
     if (dtype == MVB200_BF16) {
       return head_dim == 128 ? launch_fast<__nv_bfloat16, 128>(p, k_cache, v_cache, block_size, s)

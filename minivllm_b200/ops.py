@@ -254,8 +254,13 @@ def paged_decode_attention(
     num_splits: int | None = None,
     workspace: torch.Tensor | None = None,
     out: torch.Tensor | None = None,
+    kv_prefix_stable: bool = False,
 ) -> torch.Tensor:
     """``softmax(scale * q K^T) V`` of one query token per sequence over paged KV.
+
+    ``kv_prefix_stable=True`` (``MVB200_DECODE_KV_PREFIX_STABLE``): the kernel launched just before this call
+    writes nothing but the newest token of each sequence (and q) — the kernel may then fetch older K/V tiles
+    before that predecessor has finished (programmatic dependent launch).
 
     ``q [B, H, D]``, caches ``[NB, BS, KVH, D]``, ``block_tables [B, MB]`` int32,
     ``context_lens [B]`` int32 (current token included).  Returns ``[B, H, D]``.
@@ -310,13 +315,13 @@ def paged_decode_attention(
             raise ValueError(f"decode workspace too small: need {need} float32 (ops.decode_workspace)")
         if workspace is not None:
             ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
-    rc = _native.lib().mvb200_paged_decode(
+    rc = _native.lib().mvb200_paged_decode_ex(
         q.data_ptr(), _row_stride(q), k_cache.data_ptr(), v_cache.data_ptr(),
         block_tables.data_ptr() if mb > 0 else 0, block_tables.stride(0) if mb > 0 else 0,
         context_lens.data_ptr(), out.data_ptr(), h * d, ws_ptr, ws_bytes,
-        b, h, kvh, d, bs, nb, mb, num_splits, float(scale), _code(q.dtype), _stream(),
+        b, h, kvh, d, bs, nb, mb, num_splits, float(scale), _code(q.dtype), 1 if kv_prefix_stable else 0, _stream(),
     )
-    _native.check(rc, "mvb200_paged_decode")
+    _native.check(rc, "mvb200_paged_decode_ex")
     return out
 
 

@@ -26,7 +26,7 @@ def _declared_symbols():
 
 def test_header_declares_the_hot_path():
     syms = _declared_symbols()
-    for want in ("mvb200_store_kvcache", "mvb200_paged_decode", "mvb200_prefill_varlen",
+    for want in ("mvb200_store_kvcache", "mvb200_paged_decode", "mvb200_paged_decode_ex", "mvb200_prefill_varlen",
                  "mvb200_decode_workspace_bytes", "mvb200_decode_suggest_splits",
                  "mvb200_version", "mvb200_last_error", "mvb200_last_kernel"):
         assert want in syms
@@ -37,7 +37,7 @@ def test_library_exports_every_declared_symbol(native):
     for sym in _declared_symbols():
         assert hasattr(handle, sym), f"{sym} declared in mvb200.h but not exported"
     assert sorted(native.SIGNATURES) == _declared_symbols()
-    assert native.lib().mvb200_version() == 120
+    assert native.lib().mvb200_version() == 130
 
 
 def test_host_side_helpers_need_no_gpu(native):

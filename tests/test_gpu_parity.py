@@ -352,6 +352,68 @@ def test_decode_persistent_kernel_reuses_one_workspace(m, cuda_device):
     assert (out.float() - want.float()).abs().max().item() <= 1e-2
 
 
+@pytest.mark.parametrize("batch,kvh,g,splits", [(1, 4, 7, 37), (8, 8, 4, 4), (64, 2, 8, 1), (3, 1, 2, 2)])
+def test_decode_run_ahead_under_dependent_launch(m, cuda_device, batch, kvh, g, splits):
+    """``kv_prefix_stable=True`` (MVB200_DECODE_KV_PREFIX_STABLE): the producer warp fetches the older K/V tiles of
+    its first unit before the dependency wait, i.e. while the store of the step's new tokens (the launch before
+    it) is still running.  Several captured [store -> decode] steps back to back, the new token always in each
+    sequence's last tile (block boundaries crossed on the way): every step must equal the same chain run without
+    the flag, bit for bit, and the oracle."""
+    d, bs, steps = 128, 64, 6
+    h = kvh * g
+    rng = np.random.default_rng(batch * 7 + splits)
+    ctx0 = rng.integers(60, 700, batch).tolist()
+    ctx0[0] = 63  # crosses into a new block at step 2
+    kc, vc, bt, _ = _random_paged(cuda_device, batch, [c + steps + 1 for c in ctx0], kvh, d, bs, torch.bfloat16, 90 + batch)
+    ws = m.ops.decode_workspace(m.ops.decode_workspace_numel(batch, h, d, splits), cuda_device)
+    g_cpu = torch.Generator().manual_seed(batch)
+    qs = torch.randn(steps, batch, h, d, generator=g_cpu).to(torch.bfloat16).to(cuda_device)
+    ks = torch.randn(steps, batch, kvh, d, generator=g_cpu).to(torch.bfloat16).to(cuda_device)
+    vs = torch.randn(steps, batch, kvh, d, generator=g_cpu).to(torch.bfloat16).to(cuda_device)
+    lens = [torch.tensor([c + s + 1 for c in ctx0], dtype=torch.int32, device=cuda_device) for s in range(steps)]
+    rows = torch.arange(batch, device=cuda_device)
+    slots = [(bt[rows, (ln.long() - 1) // bs].long() * bs + (ln.long() - 1) % bs).to(torch.int32) for ln in lens]
+
+    def chain(flag, kcache, vcache):
+        outs = torch.empty(steps, batch, h, d, dtype=torch.bfloat16, device=cuda_device)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        graph = torch.cuda.CUDAGraph()
+
+        def body():
+            for s in range(steps):
+                m.store_kvcache(ks[s], vs[s], kcache, vcache, slots[s])
+                m.paged_decode_attention(qs[s], kcache, vcache, bt, lens[s], d**-0.5, num_splits=splits, workspace=ws,
+                                         out=outs[s], kv_prefix_stable=flag)
+
+        k0, v0 = kcache.clone(), vcache.clone()
+        with torch.cuda.stream(side):
+            body()  # warm-up (eager launches are chained with dependent launch as well)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        eager = outs.clone()
+        kcache.copy_(k0)
+        vcache.copy_(v0)
+        with torch.cuda.graph(graph):
+            body()
+        for _ in range(3):
+            kcache.copy_(k0)
+            vcache.copy_(v0)
+            graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(outs, eager)
+        return outs
+
+    plain = chain(False, kc.clone(), vc.clone())
+    kc2, vc2 = kc.clone(), vc.clone()
+    ahead = chain(True, kc2, vc2)
+    assert torch.equal(ahead, plain)
+    pick = sorted({0, batch // 2, batch - 1})
+    o = orc.paged_decode(_f32(qs[-1][pick]), _f32(kc2), _f32(vc2), bt[pick].cpu().numpy(),
+                         lens[-1][pick].cpu().numpy(), d**-0.5)
+    assert np.abs(_f32(ahead[-1][pick]) - o).max() <= TOL["bf16"]
+
+
 # ---------------------------------------------------------------------------
 # prefill
 # ---------------------------------------------------------------------------

@@ -2,7 +2,7 @@
 # One evidence run on the B200 box (under gpurun, one GPU): GPU tests, smoke, both bench arms, helper-kernel
 # table, per-shape decode lines, ncu launch list + full captures.  Everything lands in gpurun_out/<tag>_*.
 # usage: tools/gpu_round.sh <tag> [stages...]
-#   stages: tests smoke bench ref aux shapes ncu_decode ncu_shapes ncu_store ncu_prefill
+#   stages: tests smoke bench ref aux shapes decode_sweep ncu_decode ncu_shapes ncu_store ncu_prefill
 set -u
 TAG=${1:-run}; shift || true
 STAGES=${*:-tests smoke bench ref aux shapes ncu_decode ncu_shapes ncu_store}
@@ -36,6 +36,28 @@ if has shapes; then
     timeout 300 python bench.py --no-cpu-baseline --steps 8 --warmup 3 --workload $wl 2>>$O/${TAG}_shapes.err | python tools/bench_line.py $wl >> $O/${TAG}_shapes.jsonl
   done
   cat $O/${TAG}_shapes.jsonl
+fi
+if has decode_sweep; then
+  : > $O/${TAG}_decode_sweep.jsonl
+  sw() { label=$1; wl=$2; shift 2
+    env "$@" timeout 300 python bench.py --no-cpu-baseline --steps 20 --warmup 3 --workload $wl ${EXTRA:-} 2>>$O/${TAG}_sweep.err | python tools/bench_line.py $label >> $O/${TAG}_decode_sweep.jsonl
+  }
+  sw cfg4_default cfg4 A=1
+  sw cfg4_noearly cfg4 MVB200_DECODE_NO_EARLY=1
+  EXTRA="--splits 37" sw cfg4_s37 cfg4 A=1
+  EXTRA="--splits 37" sw cfg4_s37_1cta cfg4 MVB200_DECODE_CTAS_PER_SM=1
+  EXTRA="--splits 37" sw cfg4_s37_1cta_4st cfg4 MVB200_DECODE_CTAS_PER_SM=1 MVB200_DECODE_STAGES=4
+  sw cfg4_kernel_reduce cfg4 MVB200_DECODE_REDUCE=kernel
+  sw cfg3d_default cfg3d A=1
+  sw cfg3d_noearly cfg3d MVB200_DECODE_NO_EARLY=1
+  EXTRA="--splits 2" sw cfg3d_s2 cfg3d A=1
+  EXTRA="--splits 2" sw cfg3d_s2_1cta cfg3d MVB200_DECODE_CTAS_PER_SM=1
+  EXTRA="--splits 1" sw cfg3d_s1 cfg3d A=1
+  sw cfg2tp8_default cfg2tp8 A=1
+  sw cfg2tp8_noearly cfg2tp8 MVB200_DECODE_NO_EARLY=1
+  sw cfg5d_default cfg5d A=1
+  sw cfg2_default cfg2 A=1
+  cat $O/${TAG}_decode_sweep.jsonl
 fi
 NCU="ncu --clock-control none"
 if has ncu_decode; then
