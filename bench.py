@@ -527,7 +527,7 @@ def run_decode(env: Env, args, wl, wl_key) -> dict:
 
     bytes_layer_rank = kv_bytes_per_layer(ctx_sum, KVH, D)
     bytes_step_job = bytes_layer_rank * L * tp
-    launches_per_step = L * 2  # store_kvcache + paged_decode (the split reduction is fused into the decode kernel)
+    launches_per_step = L  # one paged_decode launch per layer: the store of the new tokens and the split reduction are fused into it
     peaks = load_peaks()
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_layer_rank / (ms_dec / L * 1e-3) / 1e9

@@ -124,7 +124,20 @@ MVB200_API int mvb200_paged_decode(const void* q, int64_t q_row_stride,
  * streaming the older K/V tiles while that predecessor is still draining. */
 #define MVB200_DECODE_KV_PREFIX_STABLE 1u
 
-/* mvb200_paged_decode with flags (0 = the call above). */
+/* The step's new tokens, to be stored by the decode kernel itself (fused store_kvcache, saves one launch per
+ * layer): row b of key/value [B, KVH, D] goes to slot_mapping[b] when 0 <= slot < num_blocks * block_size,
+ * bits moved unchanged, exactly as mvb200_store_kvcache would.  slot_mapping[b] must be the slot of position
+ * context_lens[b] - 1 of sequence b (what _prepare_decode_input produces, inference_executor.py:568-572) or
+ * negative (padding row).  Shapes the fused path does not cover fall back to a separate store launch. */
+typedef struct mvb200_decode_store {
+  const void* key;
+  const void* value;
+  int64_t key_row_stride;   /* elements between token rows */
+  int64_t value_row_stride;
+  const int32_t* slot_mapping;
+} mvb200_decode_store;
+
+/* mvb200_paged_decode with flags and an optional fused store (flags = 0, store = NULL: the call above). */
 MVB200_API int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride,
                            const void* k_cache, const void* v_cache,
                            const int32_t* block_tables, int64_t bt_row_stride,
@@ -133,7 +146,8 @@ MVB200_API int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride,
                            void* workspace, size_t workspace_bytes,
                            int32_t batch, int32_t num_heads, int32_t num_kv_heads, int32_t head_dim,
                            int32_t block_size, int64_t num_blocks, int32_t max_blocks_per_seq,
-                           int32_t num_splits, float scale, int32_t dtype, uint32_t flags, void* stream);
+                           int32_t num_splits, float scale, int32_t dtype, uint32_t flags,
+                           const mvb200_decode_store* store, void* stream);
 
 /*
  * varlen causal prefill attention.

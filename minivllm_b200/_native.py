@@ -11,6 +11,13 @@ import ctypes
 import os
 from ctypes import c_char_p, c_float, c_int32, c_int64, c_size_t, c_uint32, c_void_p
 
+
+class DecodeStore(ctypes.Structure):
+    """``mvb200_decode_store`` (include/mvb200.h): the step's new tokens for the fused store of ``mvb200_paged_decode_ex``."""
+
+    _fields_ = [("key", c_void_p), ("value", c_void_p), ("key_row_stride", c_int64), ("value_row_stride", c_int64),
+                ("slot_mapping", c_void_p)]
+
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # MVB200_LIB points debugging tools at an instrumented build of the same sources (tools/prefill_trace.py)
 LIB_PATH = os.environ.get("MVB200_LIB") or os.path.join(_HERE, "libmvb200.so")
@@ -43,7 +50,7 @@ SIGNATURES = {
         [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
          c_void_p, c_int64, c_void_p, c_size_t,
          c_int32, c_int32, c_int32, c_int32, c_int32, c_int64, c_int32,
-         c_int32, c_float, c_int32, c_uint32, c_void_p],
+         c_int32, c_float, c_int32, c_uint32, c_void_p, c_void_p],
     ),
     "mvb200_prefill_varlen": (
         c_int32,

@@ -115,11 +115,17 @@ class Attention(nn.Module):
         if has_cache and q.dtype != k_cache.dtype:  # attention.py:229-234
             q, k, v = q.to(k_cache.dtype), k.to(k_cache.dtype), v.to(k_cache.dtype)
 
+        fuse_store = None
         if has_cache:
             self._cache_initialized = True
             slots = context.slot_mapping
             if not stored and slots is not None and slots.numel() > 0:  # attention.py:237-243
-                ops.store_kvcache(k, v, k_cache, v_cache, slots)
+                if (not context.is_prefill and context.block_tables is not None and context.context_lens is not None
+                        and context.block_tables.dim() == 2 and context.block_tables.size(1) > 0
+                        and slots.numel() == q.size(0) and k.dim() == 3):
+                    fuse_store = (k, v, slots)  # decode: the attention kernel stores the new token itself
+                else:
+                    ops.store_kvcache(k, v, k_cache, v_cache, slots)
         elif not context.is_prefill and not self._cache_initialized:
             raise RuntimeError(
                 "KV cache has not been initialized. Ensure ModelRunner.allocate_kv_cache() "
@@ -159,6 +165,7 @@ class Attention(nn.Module):
             # the launch before this one is the store of the step's new tokens (one slot per sequence, the
             # newest position: inference_executor.py:568-572) or nothing of ours at all
             kv_prefix_stable=True,
+            **({"new_key": fuse_store[0], "new_value": fuse_store[1], "slot_mapping": fuse_store[2]} if fuse_store else {}),
         )
 
 

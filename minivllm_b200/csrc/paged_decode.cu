@@ -71,6 +71,14 @@ struct DecodeParams {
   int32_t total_units;  // B * num_splits * KVH
   int32_t q_bulk;       // Q rows of a unit can be fetched with one 16-byte-aligned bulk copy
   int32_t early;        // MVB200_DECODE_KV_PREFIX_STABLE: K/V tiles may be fetched before the dependency wait
+  // fused store of the step's new tokens (nullptr: the caller stored them): row b goes to slot_mapping[b]
+  const void* new_k;
+  const void* new_v;
+  int64_t new_k_stride, new_v_stride;  // elements between token rows
+  const int32_t* slot_mapping;
+  void* k_cache;
+  void* v_cache;
+  int64_t num_slots;
   float scale_log2;
 };
 
@@ -89,6 +97,7 @@ MVB_DEV void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_
       "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar)
       : "memory");
 }
+MVB_DEV void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 MVB_DEV void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
 MVB_DEV float ld_cg_f32(const float* p) {
   float v;
@@ -245,6 +254,27 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
             pdl_launch_dependents();
             waited = true;
           }
+          if (p.new_k != nullptr && t0 + idx == n_tiles - 1) {
+            // Fused store_kvcache (attention_backend.py:237-266): the unit that reads a sequence's last tile
+            // first puts the new token's K/V of its kv head there — 16-byte vectors, bits moved as they are —
+            // and orders those generic-proxy writes before the TMA (async proxy) read of the tile.
+            const int64_t slot = __ldg(p.slot_mapping + b);
+            if (slot >= 0 && slot < p.num_slots) {
+              constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
+              for (int v = lane; v < 2 * kVecsPerSeg; v += 32) {
+                const bool is_v = v >= kVecsPerSeg;
+                const int c = is_v ? v - kVecsPerSeg : v;
+                const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
+                                    : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
+                T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (slot * KVH + kvh) * D;
+                reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + c);
+              }
+              __threadfence();
+              fence_proxy_async_global();
+            }
+            __syncwarp();
+            if (lane == 0) fence_proxy_async_global();
+          }
           if (lane == 0) {
             const int s = it % stages;
             const uint32_t full = bar_base + 8 * s;
@@ -272,6 +302,20 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
         pdl_wait();
         pdl_launch_dependents();
         waited = true;
+      }
+      if (p.new_k != nullptr && n_tiles == 0 && split == 0) {  // a row without context still owns a valid slot?  store it
+        const int64_t slot = __ldg(p.slot_mapping + b);
+        if (slot >= 0 && slot < p.num_slots) {
+          constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
+          for (int v = lane; v < 2 * kVecsPerSeg; v += 32) {
+            const bool is_v = v >= kVecsPerSeg;
+            const int c = is_v ? v - kVecsPerSeg : v;
+            const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
+                                : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
+            T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (slot * KVH + kvh) * D;
+            reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + c);
+          }
+        }
       }
       if (!drawn && lane == 0)
         u_next = p.sched != nullptr ? (int)gridDim.x + atomicAdd(p.sched, 1) : u + (int)gridDim.x;
@@ -890,7 +934,7 @@ extern "C" int mvb200_paged_decode(const void* q, int64_t q_row_stride, const vo
                                    int32_t dtype, void* stream) {
   return mvb200_paged_decode_ex(q, q_row_stride, k_cache, v_cache, block_tables, bt_row_stride, context_lens, out,
                                 out_row_stride, workspace, workspace_bytes, batch, num_heads, num_kv_heads, head_dim,
-                                block_size, num_blocks, max_blocks_per_seq, num_splits, scale, dtype, 0u, stream);
+                                block_size, num_blocks, max_blocks_per_seq, num_splits, scale, dtype, 0u, nullptr, stream);
 }
 
 extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const void* k_cache,
@@ -900,8 +944,29 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
                                       int32_t batch, int32_t num_heads, int32_t num_kv_heads,
                                       int32_t head_dim, int32_t block_size, int64_t num_blocks,
                                       int32_t max_blocks_per_seq, int32_t num_splits, float scale,
-                                      int32_t dtype, uint32_t flags, void* stream) {
+                                      int32_t dtype, uint32_t flags, const mvb200_decode_store* store,
+                                      void* stream) {
   using namespace mvb200;
+  if (store != nullptr && batch > 0 && k_cache && v_cache && num_blocks > 0) {
+    if (!store->key || !store->value || !store->slot_mapping)
+      return fail(MVB200_EINVAL, "paged_decode: fused store with a null pointer");
+    const int e = dtype == MVB200_F32 ? 4 : 2;
+    const bool fusable = e == 2 && (head_dim == 64 || head_dim == 128) && block_size % 64 == 0 && max_blocks_per_seq > 0 &&
+                         num_kv_heads > 0 && num_heads % num_kv_heads == 0 && num_heads / num_kv_heads <= 16 &&
+                         ((uintptr_t)store->key % 16 == 0) && ((uintptr_t)store->value % 16 == 0) &&
+                         store->key_row_stride % 8 == 0 && store->value_row_stride % 8 == 0 &&
+                         ((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) && ((uintptr_t)q % 4 == 0) &&
+                         (q_row_stride % 2 == 0) && num_blocks < (1LL << 31) && getenv("MVB200_DECODE_NO_FUSED_STORE") == nullptr;
+    if (!fusable) {
+      const int rc = mvb200_store_kvcache(store->key, store->value, store->key_row_stride, store->value_row_stride,
+                                          (void*)k_cache, (void*)v_cache, store->slot_mapping, batch,
+                                          num_kv_heads * head_dim, num_blocks * (int64_t)block_size, dtype, stream);
+      if (rc) return rc;
+      store = nullptr;
+    }
+  } else {
+    store = nullptr;
+  }
   if (batch < 0 || num_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0 || block_size <= 0)
     return fail(MVB200_EINVAL, "paged_decode: bad sizes");
   if (num_heads % num_kv_heads)
@@ -976,7 +1041,19 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
     p.total_units = (int32_t)(units * num_splits);
     p.q_bulk = (((uintptr_t)q & 15) == 0 && (q_row_stride % 8) == 0) ? 1 : 0;
     static const bool no_early = getenv("MVB200_DECODE_NO_EARLY") != nullptr;
-    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early) ? 1 : 0;
+    // run-ahead pays where start-up latency shows: at most one unit per resident CTA (measured, run 7: with
+    // several units per CTA — 512 x 1024-token sequences on one kv head — it costs 7 us per launch)
+    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early &&
+               p.total_units <= (int64_t)decode_ctas_per_sm() * device_sm_count()) ? 1 : 0;
+    p.new_k = store ? store->key : nullptr;
+    p.new_v = store ? store->value : nullptr;
+    p.new_k_stride = store ? store->key_row_stride : 0;
+    p.new_v_stride = store ? store->value_row_stride : 0;
+    p.slot_mapping = store ? store->slot_mapping : nullptr;
+    p.k_cache = (void*)k_cache;
+    p.v_cache = (void*)v_cache;
+    p.num_slots = num_blocks * (int64_t)block_size;
+    if (store) note_kernel("store_fused_in_decode");
     note_kernel(num_splits > 1 ? "decode_tma_mma_fused_reduce" : "decode_tma_mma");
     if (dtype == MVB200_BF16) {
       return head_dim == 128 ? launch_fast<__nv_bfloat16, 128>(p, k_cache, v_cache, block_size, s)
@@ -984,6 +1061,12 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
     }
     return head_dim == 128 ? launch_fast<__half, 128>(p, k_cache, v_cache, block_size, s)
                            : launch_fast<__half, 64>(p, k_cache, v_cache, block_size, s);
+  }
+  if (store != nullptr) {  // the generic kernel does not store: separate launch
+    const int rc = mvb200_store_kvcache(store->key, store->value, store->key_row_stride, store->value_row_stride,
+                                        (void*)k_cache, (void*)v_cache, store->slot_mapping, batch,
+                                        num_kv_heads * head_dim, num_blocks * (int64_t)block_size, dtype, stream);
+    if (rc) return rc;
   }
   if (head_dim > 256)
     return fail(MVB200_EUNSUPPORTED, "paged_decode: head_dim %d > 256", head_dim);

@@ -16,6 +16,8 @@ Reference call sites (relative to the reference repository):
 
 from __future__ import annotations
 
+import ctypes
+
 import torch
 
 from . import _native
@@ -255,12 +257,19 @@ def paged_decode_attention(
     workspace: torch.Tensor | None = None,
     out: torch.Tensor | None = None,
     kv_prefix_stable: bool = False,
+    new_key: torch.Tensor | None = None,
+    new_value: torch.Tensor | None = None,
+    slot_mapping: torch.Tensor | None = None,
 ) -> torch.Tensor:
     """``softmax(scale * q K^T) V`` of one query token per sequence over paged KV.
 
     ``kv_prefix_stable=True`` (``MVB200_DECODE_KV_PREFIX_STABLE``): the kernel launched just before this call
     writes nothing but the newest token of each sequence (and q) — the kernel may then fetch older K/V tiles
     before that predecessor has finished (programmatic dependent launch).
+
+    ``new_key`` / ``new_value`` ``[B, KVH, D]`` + ``slot_mapping [B]``: the step's new tokens, stored into the
+    caches by the decode kernel itself (``store_kvcache`` fused in: bit-identical cache contents, one launch
+    less per layer).  ``slot_mapping[b]`` must be the slot of position ``context_lens[b] - 1`` (or negative).
 
     ``q [B, H, D]``, caches ``[NB, BS, KVH, D]``, ``block_tables [B, MB]`` int32,
     ``context_lens [B]`` int32 (current token included).  Returns ``[B, H, D]``.
@@ -315,11 +324,29 @@ def paged_decode_attention(
             raise ValueError(f"decode workspace too small: need {need} float32 (ops.decode_workspace)")
         if workspace is not None:
             ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    store = None
+    if new_key is not None:
+        if new_value is None or slot_mapping is None:
+            raise ValueError("new_key needs new_value and slot_mapping")
+        _require_cuda(new_key, new_value, slot_mapping)
+        new_key, new_value = _rows(new_key), _rows(new_value)
+        if new_key.shape != (b, kvh, d) or new_value.shape != (b, kvh, d):
+            raise ValueError(f"new_key / new_value must be [B, KVH, D] = {(b, kvh, d)}")
+        if new_key.dtype != k_cache.dtype or new_value.dtype != k_cache.dtype:
+            raise ValueError("new_key / new_value must have the cache dtype")
+        slot_mapping = _i32(slot_mapping.reshape(-1), q.device)
+        if slot_mapping.numel() != b:  # attention_backend.py:248-250
+            raise ValueError(f"slot_mapping size ({slot_mapping.numel()}) must match number of tokens ({b})")
+        if not slot_mapping.is_contiguous():
+            slot_mapping = slot_mapping.contiguous()
+        store = _native.DecodeStore(new_key.data_ptr(), new_value.data_ptr(), _row_stride(new_key), _row_stride(new_value),
+                                    slot_mapping.data_ptr())
     rc = _native.lib().mvb200_paged_decode_ex(
         q.data_ptr(), _row_stride(q), k_cache.data_ptr(), v_cache.data_ptr(),
         block_tables.data_ptr() if mb > 0 else 0, block_tables.stride(0) if mb > 0 else 0,
         context_lens.data_ptr(), out.data_ptr(), h * d, ws_ptr, ws_bytes,
-        b, h, kvh, d, bs, nb, mb, num_splits, float(scale), _code(q.dtype), 1 if kv_prefix_stable else 0, _stream(),
+        b, h, kvh, d, bs, nb, mb, num_splits, float(scale), _code(q.dtype), 1 if kv_prefix_stable else 0,
+        ctypes.byref(store) if store is not None else None, _stream(),
     )
     _native.check(rc, "mvb200_paged_decode_ex")
     return out

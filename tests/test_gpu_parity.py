@@ -414,6 +414,45 @@ def test_decode_run_ahead_under_dependent_launch(m, cuda_device, batch, kvh, g, 
     assert np.abs(_f32(ahead[-1][pick]) - o).max() <= TOL["bf16"]
 
 
+@pytest.mark.parametrize("dtype,batch,kvh,g,d,splits", [("bf16", 5, 2, 4, 128, 1), ("bf16", 1, 4, 7, 128, 9), ("f16", 33, 1, 8, 64, 2),
+                                                        ("bf16", 256, 8, 2, 128, 1), ("f32", 4, 2, 2, 64, 1)])
+def test_decode_with_fused_store(m, cuda_device, dtype, batch, kvh, g, d, splits):
+    """``paged_decode_attention(new_key=..., new_value=..., slot_mapping=...)``: the decode kernel stores the step's
+    new tokens itself.  Cache contents must be bit-identical to ``store_kvcache`` followed by the plain decode, and so
+    must the attention output (same arithmetic); padded rows (slot -1, context 0) and row-strided k/v (views of a
+    fused qkv buffer) included.  fp32 takes the generic kernel: the library stores with a separate launch."""
+    bs, h = 64, kvh * g
+    rng = np.random.default_rng(batch + splits)
+    ctxs = rng.integers(1, 400, batch).tolist()
+    if batch > 2:
+        ctxs[1] = 64   # new token is the last row of a block
+        ctxs[2] = 65   # ... the first row of a fresh block
+    kc, vc, bt, cl = _random_paged(cuda_device, batch, ctxs, kvh, d, bs, TDT[dtype], 70 + batch)
+    slots = (bt[torch.arange(batch), (cl.long() - 1) // bs].long() * bs + (cl.long() - 1) % bs).to(torch.int32)
+    if batch > 4:  # CUDA-graph padding rows
+        cl[-2:] = 0
+        slots[-2:] = -1
+    fused = torch.randn(batch, (h + 2 * kvh) * d, device=cuda_device).to(TDT[dtype])
+    q = fused[:, : h * d].view(batch, h, d)
+    k = fused[:, h * d : (h + kvh) * d].view(batch, kvh, d)
+    v = fused[:, (h + kvh) * d :].view(batch, kvh, d)
+    ws = m.ops.decode_workspace(m.ops.decode_workspace_numel(batch, h, d, splits), cuda_device)
+    k1, v1 = kc.clone(), vc.clone()
+    m.store_kvcache(k, v, k1, v1, slots)
+    want = m.paged_decode_attention(q, k1, v1, bt, cl, d**-0.5, num_splits=splits, workspace=ws)
+    k2, v2 = kc.clone(), vc.clone()
+    got = m.paged_decode_attention(q, k2, v2, bt, cl, d**-0.5, num_splits=splits, workspace=ws,
+                                   new_key=k, new_value=v, slot_mapping=slots, kv_prefix_stable=True)
+    torch.cuda.synchronize()
+    if dtype != "f32":
+        assert "store_fused_in_decode" in m.ops.kernels_seen()
+    assert np.array_equal(_bits(k2), _bits(k1)) and np.array_equal(_bits(v2), _bits(v1))
+    assert not np.array_equal(_bits(k2), _bits(kc))
+    assert torch.equal(got, want)
+    with pytest.raises(ValueError, match="slot_mapping size"):
+        m.paged_decode_attention(q, k2, v2, bt, cl, d**-0.5, new_key=k, new_value=v, slot_mapping=slots[:-1])
+
+
 # ---------------------------------------------------------------------------
 # prefill
 # ---------------------------------------------------------------------------
