@@ -219,6 +219,26 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
       const int n = max(t1 - t0, 0);
       const int32_t* bt = p.block_tables + (int64_t)b * p.bt_row_stride;
       const uint32_t q_bytes = (uint32_t)(G * D * (int)sizeof(T));
+      // Fused store_kvcache (attention_backend.py:237-266): the unit that reads a sequence's last tile puts the
+      // new token's K/V of its kv head there first — 16-byte vectors, bits moved as they are.  The stores are
+      // issued here, at the start of the unit (their latency hides behind the tiles already in the ring); the
+      // fences that order them before the TMA (async proxy) read come just before that tile is requested.
+      // (The launcher never combines the fused store with run-ahead: new_k is produced by the preceding kernels.)
+      const bool owns_last = p.new_k != nullptr && (n_tiles > 0 ? (n > 0 && t1 == n_tiles) : split == 0);
+      if (owns_last) {
+        const int64_t slot = __ldg(p.slot_mapping + b);
+        if (slot >= 0 && slot < p.num_slots) {
+          constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
+          for (int v = lane; v < 2 * kVecsPerSeg; v += 32) {
+            const bool is_v = v >= kVecsPerSeg;
+            const int c = is_v ? v - kVecsPerSeg : v;
+            const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
+                                : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
+            T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (slot * KVH + kvh) * D;
+            reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + c);
+          }
+        }
+      }
       for (int base = 0; base < n; base += 32) {
         // 32 block-table entries per coalesced load, then one lane issues the copies
         int my_bid = p.num_blocks;  // out-of-bounds coordinate: TMA fills the tile with zeros
@@ -254,24 +274,9 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
             pdl_launch_dependents();
             waited = true;
           }
-          if (p.new_k != nullptr && t0 + idx == n_tiles - 1) {
-            // Fused store_kvcache (attention_backend.py:237-266): the unit that reads a sequence's last tile
-            // first puts the new token's K/V of its kv head there — 16-byte vectors, bits moved as they are —
-            // and orders those generic-proxy writes before the TMA (async proxy) read of the tile.
-            const int64_t slot = __ldg(p.slot_mapping + b);
-            if (slot >= 0 && slot < p.num_slots) {
-              constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
-              for (int v = lane; v < 2 * kVecsPerSeg; v += 32) {
-                const bool is_v = v >= kVecsPerSeg;
-                const int c = is_v ? v - kVecsPerSeg : v;
-                const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
-                                    : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
-                T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (slot * KVH + kvh) * D;
-                reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + c);
-              }
-              __threadfence();
-              fence_proxy_async_global();
-            }
+          if (owns_last && t0 + idx == n_tiles - 1) {
+            __threadfence();
+            fence_proxy_async_global();
             __syncwarp();
             if (lane == 0) fence_proxy_async_global();
           }
@@ -302,20 +307,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
         pdl_wait();
         pdl_launch_dependents();
         waited = true;
-      }
-      if (p.new_k != nullptr && n_tiles == 0 && split == 0) {  // a row without context still owns a valid slot?  store it
-        const int64_t slot = __ldg(p.slot_mapping + b);
-        if (slot >= 0 && slot < p.num_slots) {
-          constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
-          for (int v = lane; v < 2 * kVecsPerSeg; v += 32) {
-            const bool is_v = v >= kVecsPerSeg;
-            const int c = is_v ? v - kVecsPerSeg : v;
-            const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
-                                : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
-            T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (slot * KVH + kvh) * D;
-            reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + c);
-          }
-        }
       }
       if (!drawn && lane == 0)
         u_next = p.sched != nullptr ? (int)gridDim.x + atomicAdd(p.sched, 1) : u + (int)gridDim.x;
@@ -1043,7 +1034,9 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
     static const bool no_early = getenv("MVB200_DECODE_NO_EARLY") != nullptr;
     // run-ahead pays where start-up latency shows: at most one unit per resident CTA (measured, run 7: with
     // several units per CTA — 512 x 1024-token sequences on one kv head — it costs 7 us per launch)
-    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early &&
+    // ... and never together with the fused store (whose source rows the preceding kernels produce; measured,
+    // run 8: the one-launch step is fastest without it)
+    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early && store == nullptr &&
                p.total_units <= (int64_t)decode_ctas_per_sm() * device_sm_count()) ? 1 : 0;
     p.new_k = store ? store->key : nullptr;
     p.new_v = store ? store->value : nullptr;
