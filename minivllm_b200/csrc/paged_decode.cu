@@ -212,6 +212,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
       const int split = rest % S;
       const int b = rest / S;
       const int ctx = __ldg(p.context_lens + b);
+      const int64_t new_slot = p.new_k != nullptr ? (int64_t)__ldg(p.slot_mapping + b) : -1;  // in flight with ctx
       const int n_tiles = ctx > 0 ? (ctx + kTileTokens - 1) / kTileTokens : 0;
       const int tps = (n_tiles + S - 1) / S;
       const int t0 = split * tps;
@@ -220,25 +221,27 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
       const int32_t* bt = p.block_tables + (int64_t)b * p.bt_row_stride;
       const uint32_t q_bytes = (uint32_t)(G * D * (int)sizeof(T));
       // Fused store_kvcache (attention_backend.py:237-266): the unit that reads a sequence's last tile puts the
-      // new token's K/V of its kv head there first — 16-byte vectors, bits moved as they are.  The stores are
-      // issued here, at the start of the unit (their latency hides behind the tiles already in the ring); the
-      // fences that order them before the TMA (async proxy) read come just before that tile is requested.
-      // (The launcher never combines the fused store with run-ahead: new_k is produced by the preceding kernels.)
+      // new token's K/V of its kv head there first — 16-byte vectors, bits moved as they are.  The copy is
+      // issued right after the unit's first tile has been requested (its latency then hides behind tiles in
+      // flight; a unit boundary that waits for slot -> source -> store before it refills the ring costs the
+      // big batches 1.5 %, run 9); the fences that order the stores before the TMA (async proxy) read come just
+      // before the last tile is requested.  (The launcher never combines the fused store with run-ahead: the
+      // new rows are produced by the preceding kernels.)
       const bool owns_last = p.new_k != nullptr && (n_tiles > 0 ? (n > 0 && t1 == n_tiles) : split == 0);
-      if (owns_last) {
-        const int64_t slot = __ldg(p.slot_mapping + b);
-        if (slot >= 0 && slot < p.num_slots) {
+      auto store_new_token = [&]() {
+        if (new_slot >= 0 && new_slot < p.num_slots) {
           constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
           for (int v = lane; v < 2 * kVecsPerSeg; v += 32) {
             const bool is_v = v >= kVecsPerSeg;
             const int c = is_v ? v - kVecsPerSeg : v;
             const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
                                 : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
-            T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (slot * KVH + kvh) * D;
+            T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (new_slot * KVH + kvh) * D;
             reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + c);
           }
         }
-      }
+      };
+      if (owns_last && n <= 1) store_new_token();
       for (int base = 0; base < n; base += 32) {
         // 32 block-table entries per coalesced load, then one lane issues the copies
         int my_bid = p.num_blocks;  // out-of-bounds coordinate: TMA fills the tile with zeros
@@ -301,6 +304,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
           }
           ++it;
           __syncwarp();
+          if (owns_last && n > 1 && idx == 0) store_new_token();
         }
       }
       if (!waited) {  // an empty first unit
