@@ -97,7 +97,6 @@ MVB_DEV void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_
       "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar)
       : "memory");
 }
-MVB_DEV void fence_proxy_async_global() { asm volatile("fence.proxy.async.global;" ::: "memory"); }
 MVB_DEV void consumer_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kConsumerThreads) : "memory"); }
 MVB_DEV float ld_cg_f32(const float* p) {
   float v;
@@ -212,7 +211,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
       const int split = rest % S;
       const int b = rest / S;
       const int ctx = __ldg(p.context_lens + b);
-      const int64_t new_slot = p.new_k != nullptr ? (int64_t)__ldg(p.slot_mapping + b) : -1;  // in flight with ctx
       const int n_tiles = ctx > 0 ? (ctx + kTileTokens - 1) / kTileTokens : 0;
       const int tps = (n_tiles + S - 1) / S;
       const int t0 = split * tps;
@@ -220,28 +218,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
       const int n = max(t1 - t0, 0);
       const int32_t* bt = p.block_tables + (int64_t)b * p.bt_row_stride;
       const uint32_t q_bytes = (uint32_t)(G * D * (int)sizeof(T));
-      // Fused store_kvcache (attention_backend.py:237-266): the unit that reads a sequence's last tile puts the
-      // new token's K/V of its kv head there first — 16-byte vectors, bits moved as they are.  The copy is
-      // issued right after the unit's first tile has been requested (its latency then hides behind tiles in
-      // flight; a unit boundary that waits for slot -> source -> store before it refills the ring costs the
-      // big batches 1.5 %, run 9); the fences that order the stores before the TMA (async proxy) read come just
-      // before the last tile is requested.  (The launcher never combines the fused store with run-ahead: the
-      // new rows are produced by the preceding kernels.)
-      const bool owns_last = p.new_k != nullptr && (n_tiles > 0 ? (n > 0 && t1 == n_tiles) : split == 0);
-      auto store_new_token = [&]() {
-        if (new_slot >= 0 && new_slot < p.num_slots) {
-          constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
-          for (int v = lane; v < 2 * kVecsPerSeg; v += 32) {
-            const bool is_v = v >= kVecsPerSeg;
-            const int c = is_v ? v - kVecsPerSeg : v;
-            const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
-                                : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
-            T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (new_slot * KVH + kvh) * D;
-            reinterpret_cast<uint4*>(dst)[c] = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + c);
-          }
-        }
-      };
-      if (owns_last && n <= 1) store_new_token();
       for (int base = 0; base < n; base += 32) {
         // 32 block-table entries per coalesced load, then one lane issues the copies
         int my_bid = p.num_blocks;  // out-of-bounds coordinate: TMA fills the tile with zeros
@@ -277,12 +253,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
             pdl_launch_dependents();
             waited = true;
           }
-          if (owns_last && t0 + idx == n_tiles - 1) {
-            __threadfence();
-            fence_proxy_async_global();
-            __syncwarp();
-            if (lane == 0) fence_proxy_async_global();
-          }
           if (lane == 0) {
             const int s = it % stages;
             const uint32_t full = bar_base + 8 * s;
@@ -304,7 +274,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
           }
           ++it;
           __syncwarp();
-          if (owns_last && n > 1 && idx == 0) store_new_token();
         }
       }
       if (!waited) {  // an empty first unit
@@ -345,6 +314,33 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
     const UnitInfo info = uinfo[it % stages];
     if (info.n < 0) break;
     const int b = info.b, kvh = info.kvh, split = info.split, t0 = info.t0, n = info.n, ctx = info.ctx;
+
+    // Fused store_kvcache (attention_backend.py:237-266): the unit that reads a sequence's last tile also owns
+    // the step's new token of its kv head.  The warp whose 16 tokens include it fetches the new K/V row segment
+    // at the start of the unit (one 16-byte vector per lane: K on the low lanes, V above), and when the last tile
+    // has landed writes it INTO THE TILE in shared memory (the TMA copy of that row is stale) and to its slot in
+    // the cache — plain stores, no fence on the load path: nobody else reads that row in this launch.
+    constexpr int kVecsPerSeg = D * (int)sizeof(T) / 16;
+    const int seq_tiles = ctx > 0 ? (ctx + kTileTokens - 1) / kTileTokens : 0;
+    const int new_row = (ctx - 1) & (kTileTokens - 1);
+    const bool own_new = p.new_k != nullptr && (n > 0 ? (t0 + n == seq_tiles && warp == (new_row >> 4))
+                                                      : (seq_tiles == 0 && split == 0 && warp == 0));
+    int64_t new_slot = -1;
+    uint4 new_vec = make_uint4(0, 0, 0, 0);
+    if (own_new) {
+      new_slot = __ldg(p.slot_mapping + b);
+      if (new_slot < 0 || new_slot >= p.num_slots) new_slot = -1;
+      if (new_slot >= 0 && lane < 2 * kVecsPerSeg) {
+        const bool is_v = lane >= kVecsPerSeg;
+        const T* src = is_v ? reinterpret_cast<const T*>(p.new_v) + (int64_t)b * p.new_v_stride
+                            : reinterpret_cast<const T*>(p.new_k) + (int64_t)b * p.new_k_stride;
+        new_vec = __ldg(reinterpret_cast<const uint4*>(src + (int64_t)kvh * D) + (is_v ? lane - kVecsPerSeg : lane));
+        if (n == 0) {  // a row without context: nothing to attend to, the cache still gets the token
+          T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (new_slot * KVH + kvh) * D;
+          reinterpret_cast<uint4*>(dst)[is_v ? lane - kVecsPerSeg : lane] = new_vec;
+        }
+      }
+    }
 
     float o_acc[D / 8][4];
     float m_run[2] = {-INFINITY, -INFINITY};
@@ -390,6 +386,19 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
         const bool partial = tile_tok0 + kTileTokens > ctx;
 
         if (j > 0) mbar_wait(full, (it / stages) & 1);
+
+        if (own_new && j == n - 1 && new_slot >= 0) {
+          if (lane < 2 * kVecsPerSeg) {
+            const bool is_v = lane >= kVecsPerSeg;
+            const int c = is_v ? lane - kVecsPerSeg : lane;
+            uint8_t* tile = smem_gen + ((is_v ? vbase : kbase) - smem_base);
+            *reinterpret_cast<uint4*>(tile + (c >> 3) * kHalfBytes + new_row * 128 + (((c & 7) ^ (new_row & 7)) << 4)) = new_vec;
+            T* dst = reinterpret_cast<T*>(is_v ? p.v_cache : p.k_cache) + (new_slot * KVH + kvh) * D;
+            reinterpret_cast<uint4*>(dst)[c] = new_vec;
+          }
+          fence_proxy_async_smem();  // generic writes before the next TMA refill of this slot
+          __syncwarp();
+        }
 
         // ---- S = Q K^T for this warp's 16 tokens ----
         float sacc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
