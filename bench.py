@@ -463,9 +463,11 @@ def run_decode(env: Env, args, wl, wl_key) -> dict:
         m.set_context(False, slot_mapping=sl, context_lens=cl, block_tables=bt,
                       decode_num_splits=splits, decode_workspace=workspace)
 
-    def full_step():  # the hot path of one decode step: store + paged decode, every layer
-        for l, a in enumerate(layers):
-            outs[l] = a(q, k, v)
+    def full_step():  # the hot path of one decode step: store + paged decode, every layer (one launch each)
+        o = None
+        for a in layers:
+            o = a(q, k, v)  # the layer's own output tensor, as the model consumes it (no copy kernel in between)
+        return o
 
     def decode_only():
         for l, a in enumerate(layers):
