@@ -18,6 +18,7 @@ SOURCES = [
     "paged_decode.cu",
     "prefill_generic.cu",
     "prefill_fa2q.cu",
+    "prefill_dbs.cu",
     "prefill_api.cu",
 ]
 # tuning build only (--trace): the first-generation prefill kernel and the knob matrix of the 2q kernel

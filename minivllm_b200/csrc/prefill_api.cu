@@ -18,6 +18,7 @@ int prefill_generic_dispatch(const void* q, int64_t q_row_stride, const void* k,
 
 // return -1 when the request is outside what the kernel covers
 int prefill_fa2q_dispatch(const PrefillArgs& a, cudaStream_t stream);     // persistent, two query tiles per CTA
+int prefill_dbs_dispatch(const PrefillArgs& a, cudaStream_t stream);      // + 64-key steps with double-buffered S
 #ifdef MVB200_TUNING
 // first-generation kernel (one query tile per CTA): A/B tool of the tuning build only
 // (python minivllm_b200/build.py --trace), not part of libmvb200.so
@@ -61,14 +62,24 @@ extern "C" int mvb200_prefill_varlen(
   const bool force_generic = getenv("MVB200_PREFILL_GENERIC") != nullptr;
   const bool force_v1 = getenv("MVB200_PREFILL_V1") != nullptr;
   if (!force_generic) {
-    int rc = force_v1 ? -1 : prefill_fa2q_dispatch(a, s);
+    const char* which = getenv("MVB200_PREFILL_KERNEL");
+    int rc = (!force_v1 && which && which[0] == 'd') ? prefill_dbs_dispatch(a, s) : -1;
+    if (rc >= 0) return rc;
+    rc = force_v1 ? -1 : prefill_fa2q_dispatch(a, s);
     if (rc >= 0) return rc;
     rc = prefill_tcgen05_dispatch(a, s);
     if (rc >= 0) return rc;
   }
 #else
   {
-    const int rc = prefill_fa2q_dispatch(a, s);
+    // MVB200_PREFILL_KERNEL = dbs | fa2q (A/B of the two tcgen05 kernels while the newer one is being measured)
+    static const bool use_dbs = [] {
+      const char* e = getenv("MVB200_PREFILL_KERNEL");
+      return e ? e[0] == 'd' : false;
+    }();
+    int rc = use_dbs ? prefill_dbs_dispatch(a, s) : -1;
+    if (rc >= 0) return rc;
+    rc = prefill_fa2q_dispatch(a, s);
     if (rc >= 0) return rc;
   }
 #endif
