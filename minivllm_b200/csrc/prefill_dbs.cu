@@ -20,8 +20,8 @@
 //     tensor pipe alternates between the two chains.
 // Cost: S = Q K^T with N = 64 runs at 2/3 rate (192 B/clk of shared-memory operand reads against a
 // 128 B/clk limit, probes/umma_pacing), i.e. 640 instead of 512 pipe clocks per 64 keys and tile.
-// Roles (384 threads): warp 0 TMA producer, warp 1 MMA issuer, warps 2-3 idle, warps 4-7 / 8-11 the
-// softmax warpgroups of query tiles 0 / 1 (thread = query row).
+// Roles (384 threads): warp 0 TMA producer, warps 1 / 2 MMA issuers of query tiles 0 / 1, warp 3 idle,
+// warps 4-7 / 8-11 the softmax warpgroups of query tiles 0 / 1 (thread = query row).
 // Tensor-bound: 4*D flops per unmasked (q,k) pair per head.
 #include <math.h>
 #include <stdlib.h>
@@ -68,8 +68,9 @@ enum {
   BAR_V_EMPTY = BAR_V_FULL + kStages,
   BAR_S_FULL = BAR_V_EMPTY + kStages,   // [2 tiles][2 buffers]  MMA -> softmax warpgroup t
   BAR_P_FULL = BAR_S_FULL + 4,          // [2 tiles][2 buffers]  softmax warpgroup t (4 warp arrivals) -> MMA
-  BAR_O_DONE = BAR_P_FULL + 4,          // [2]  MMA (commit after every P_t V) -> softmax warpgroup t
-  BAR_COUNT = BAR_O_DONE + 2
+  BAR_O_DONE = BAR_P_FULL + 4,          // [2]  MMA (commit after every P_t V) -> softmax warpgroup t (lazy rescale)
+  BAR_O_FINAL = BAR_O_DONE + 2,         // [2]  MMA (commit after the item's last P_t V) -> softmax warpgroup t (epilogue)
+  BAR_COUNT = BAR_O_FINAL + 2
 };
 
 struct Params {
@@ -157,7 +158,8 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
   }
   if (threadIdx.x == 32) {
     for (int i = 0; i < BAR_COUNT; ++i)
-      mbar_init(bar(i), (i >= BAR_P_FULL && i < BAR_P_FULL + 4) ? 4 : 1);
+      mbar_init(bar(i), (i >= BAR_P_FULL && i < BAR_P_FULL + 4) ? 4
+                        : ((i >= BAR_K_EMPTY && i < BAR_K_EMPTY + kStages) || (i >= BAR_V_EMPTY && i < BAR_V_EMPTY + kStages)) ? 2 : 1);
     fence_mbar_init();
   }
   tc_fence_before();
@@ -238,98 +240,98 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
         __syncwarp();
       }
     }
-  } else if (warp == 1) {
-    // =========================== MMA issuer ===========================
-    // Per query tile t the chain is  QK(0) QK(1) | wait P(0): P(0)V, QK(2) | wait P(1): P(1)V, QK(3) | ...
-    // The two chains interleave step by step; every wait is a blocking one in that order (the chains run
-    // half a step apart).  Step x of a chain (counted across items) uses S buffer x & 1.
+  } else if (warp == 1 || warp == 2) {
+    // =========================== MMA issuers: warp 1 drives query tile 0, warp 2 query tile 1 ===========================
+    // Per query tile the chain is  QK(0) QK(1) | wait P(0): P(0)V, QK(2) | wait P(1): P(1)V, QK(3) | ...
+    // (step x of a chain, counted across items, uses S buffer x & 1).  tcgen05.mma from one thread executes in
+    // issue order, which is what keeps QK(j+2) behind the P(j)V that still reads its buffer; the two chains have
+    // nothing to order between them, so each gets its own issuing thread: neither waits on the other's P, and
+    // the 60-clock issue-to-issue latency of an N = 64 SS MMA (probes/umma_pacing: 60.6 clocks from one issuer,
+    // 48 from two) overlaps with the other chain's work.  A K/V stage is released by two arrivals, one per
+    // chain: a tcgen05.commit where the chain read the tile, a plain arrive (after the tile has landed, i.e. in
+    // the right barrier phase) where it did not.
+    const int t = warp - 1;
     constexpr uint32_t idesc_qk = umma_idesc(kBM, kBN, kBf16, false, false);
     constexpr uint32_t idesc_pv = umma_idesc(kBM, kD, kBf16, false, true);
     constexpr uint32_t desc_hi = umma_desc_hi(1024);  // 8-row (K-major) / 8-key (MN-major) groups 1 KiB apart
-    const uint32_t q_lo0 = umma_desc_lo(sQ, 16);
+    const uint32_t q_lo = umma_desc_lo(sQ, 16) + t * (kQTileBytes >> 4);
     const uint32_t k_lo0 = umma_desc_lo(sK, 16);
     const uint32_t v_lo0 = umma_desc_lo(sV, kKVHalfBytes);  // LBO = distance between the 64-column halves
-    uint32_t q_uses[kQTiles] = {0, 0};
-    uint32_t gq[kQTiles] = {0, 0};  // Q_t K^T issued so far (= step index of the next one)
-    uint32_t gp[kQTiles] = {0, 0};  // P_t V issued so far
+    const uint32_t s_base = tmem + kColS + t * 128;
+    const uint32_t o_col = tmem + kColO + t * kD;
+    uint32_t q_uses = 0;
+    uint32_t gq = 0;  // Q K^T issued so far (= step index of the next one)
+    uint32_t gp = 0;  // P V issued so far
     uint32_t kv_cnt = 0;
 
     for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
       const Item it = decode_item(p, w);
       if (!it.valid || it.n_kt == 0) continue;
-      int k_ready = 0;  // K tiles of this item whose arrival has been awaited
-      // S_t(jj) = Q_t K(jj)^T : 8 k-steps of 16 elements (32 B inside the 128-B swizzle row, halves apart)
-      auto issue_qk = [&](int t, int jj) {
-        while (k_ready <= jj) {
-          const uint32_t cnt = kv_cnt + k_ready;
-          mbar_wait(bar(BAR_K_FULL + cnt % kStages), (cnt / kStages) & 1);
-          ++k_ready;
-        }
+      const int n_t = t ? it.n[1] : it.n[0];
+      const int kv_end_t = t ? it.kv_end[1] : it.kv_end[0];
+      // S(jj) = Q K(jj)^T : 8 k-steps of 16 elements (32 B inside the 128-B swizzle row, halves apart)
+      auto issue_qk = [&](int jj) {
+        const uint32_t cnt = kv_cnt + jj;
+        const int s = cnt % kStages;
+        mbar_wait(bar(BAR_K_FULL + s), (cnt / kStages) & 1);
         tc_fence_after();
-        const int s = (kv_cnt + jj) % kStages;
-        const int n_t = t ? it.n[1] : it.n[0];
-        const bool last_k = (t == kQTiles - 1) || (jj >= it.n[1]);
         if (elect_one()) {
-          const uint32_t q_lo = q_lo0 + t * (kQTileBytes >> 4);
           const uint32_t k_lo = k_lo0 + s * (kKVTileBytes >> 4);
-          const uint32_t s_col = tmem + kColS + t * 128 + (gq[t] & 1) * kBN;
+          const uint32_t s_col = s_base + (gq & 1) * kBN;
 #pragma unroll
           for (int kk = 0; kk < kD / 16; ++kk) {
             const uint32_t qoff = ((kk >> 2) * kQHalfBytes + (kk & 3) * 32) >> 4;
             const uint32_t koff = ((kk >> 2) * kKVHalfBytes + (kk & 3) * 32) >> 4;
             umma_ss(s_col, umma_desc(desc_hi, q_lo + qoff), umma_desc(desc_hi, k_lo + koff), idesc_qk, kk > 0 ? 1u : 0u);
           }
-          umma_commit(bar(BAR_S_FULL + t * 2 + (gq[t] & 1)));
+          umma_commit(bar(BAR_S_FULL + t * 2 + (gq & 1)));
+          umma_commit(bar(BAR_K_EMPTY + s));
           if (jj == n_t - 1) umma_commit(bar(BAR_Q_EMPTY + t));
-          if (last_k) umma_commit(bar(BAR_K_EMPTY + s));
         }
         __syncwarp();
-        ++gq[t];
+        ++gq;
       };
 
-      // ---- prologue: S_t(0), S_t(1) ----
-#pragma unroll
-      for (int t = 0; t < kQTiles; ++t) {
-        if (it.n[t] == 0) continue;
-        mbar_wait(bar(BAR_Q_FULL + t), q_uses[t] & 1);
-        ++q_uses[t];
+      if (n_t > 0) {
+        mbar_wait(bar(BAR_Q_FULL + t), q_uses & 1);
+        ++q_uses;
+        issue_qk(0);
+        if (n_t > 1) issue_qk(1);
       }
-      for (int jj = 0; jj < 2; ++jj)
-#pragma unroll
-        for (int t = 0; t < kQTiles; ++t)
-          if (jj < it.n[t]) issue_qk(t, jj);
-
-      // ---- main loop ----
-      for (int j = 0; j < it.n_kt; ++j) {
+      for (int j = 0; j < n_t; ++j) {
         const uint32_t cnt = kv_cnt + j;
         const int s = cnt % kStages;
+        const int ksteps = j + 1 < n_t ? kBN / 16 : (kv_end_t - j * kBN + 15) / 16;
         mbar_wait(bar(BAR_V_FULL + s), (cnt / kStages) & 1);
+        mbar_wait(bar(BAR_P_FULL + t * 2 + (gp & 1)), (gp >> 1) & 1);
+        tc_fence_after();
+        if (elect_one()) {
+          // A = bf16 P in TMEM (8 columns per 16 keys), B = V MN-major, 16 keys = 2 KiB
+          const uint32_t v_lo = v_lo0 + s * (kKVTileBytes >> 4);
+          const uint32_t p_col = s_base + (gp & 1) * kBN;
 #pragma unroll
-        for (int t = 0; t < kQTiles; ++t) {
-          if (j >= it.n[t]) continue;
-          const int n_t = it.n[t];
-          const bool last_v = (t == kQTiles - 1) || (j >= it.n[1]);
-          const int ksteps = j + 1 < n_t ? kBN / 16 : (it.kv_end[t] - j * kBN + 15) / 16;
-          mbar_wait(bar(BAR_P_FULL + t * 2 + (gp[t] & 1)), (gp[t] >> 1) & 1);
-          tc_fence_after();
-          if (elect_one()) {
-            // A = bf16 P in TMEM (8 columns per 16 keys), B = V MN-major, 16 keys = 2 KiB
-            const uint32_t v_lo = v_lo0 + s * (kKVTileBytes >> 4);
-            const uint32_t p_col = tmem + kColS + t * 128 + (gp[t] & 1) * kBN;
-            const uint32_t o_col = tmem + kColO + t * kD;
-#pragma unroll
-            for (int kk = 0; kk < kBN / 16; ++kk) {
-              if (kk < ksteps)
-                umma_ts(o_col, p_col + kk * 8, umma_desc(desc_hi, v_lo + kk * (16 * 128 >> 4)), idesc_pv,
-                        (j > 0 || kk > 0) ? 1u : 0u);
-            }
-            umma_commit(bar(BAR_O_DONE + t));
-            if (last_v) umma_commit(bar(BAR_V_EMPTY + s));
+          for (int kk = 0; kk < kBN / 16; ++kk) {
+            if (kk < ksteps)
+              umma_ts(o_col, p_col + kk * 8, umma_desc(desc_hi, v_lo + kk * (16 * 128 >> 4)), idesc_pv,
+                      (j > 0 || kk > 0) ? 1u : 0u);
           }
-          __syncwarp();
-          ++gp[t];
-          if (j + 2 < n_t) issue_qk(t, j + 2);
+          umma_commit(bar(BAR_O_DONE + t));
+          umma_commit(bar(BAR_V_EMPTY + s));
+          if (j == n_t - 1) umma_commit(bar(BAR_O_FINAL + t));
         }
+        __syncwarp();
+        ++gp;
+        if (j + 2 < n_t) issue_qk(j + 2);
+      }
+      // tiles only the other chain reads: hand this chain's share of the release over once they have landed
+      for (int j = n_t; j < it.n_kt; ++j) {
+        const uint32_t cnt = kv_cnt + j;
+        const int s = cnt % kStages;
+        mbar_wait(bar(BAR_K_FULL + s), (cnt / kStages) & 1);
+        if (lane == 0) mbar_arrive(bar(BAR_K_EMPTY + s));
+        mbar_wait(bar(BAR_V_FULL + s), (cnt / kStages) & 1);
+        if (lane == 0) mbar_arrive(bar(BAR_V_EMPTY + s));
+        __syncwarp();
       }
       kv_cnt += it.n_kt;
     }
@@ -345,6 +347,7 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const uint32_t o_col = lane_base + kColO + t * kD;
     T* out = reinterpret_cast<T*>(p.out);
     uint32_t g = 0;        // steps consumed by this warpgroup so far (S buffer g & 1; = P V commits it may wait for)
+    uint32_t items_done = 0;  // items whose O this warpgroup has written out (phase of BAR_O_FINAL)
     uint32_t kv_cnt = 0;   // K/V tiles streamed by the CTA before the current item
 
     for (int w = blockIdx.x; w < total_items; w += gridDim.x) {
@@ -474,7 +477,10 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
       }
 
       // ---- epilogue: O / l -> global ----
-      mbar_wait(bar(BAR_O_DONE + t), (g - 1) & 1);
+      // (not BAR_O_DONE: with S two steps ahead this warpgroup may be two P V commits behind, and a parity wait
+      // can only tell one phase from the next)
+      mbar_wait(bar(BAR_O_FINAL + t), items_done & 1);
+      ++items_done;
       tc_fence_after();
       // a row that sees no key (Lk < Lq) still sums 2^-126 per FMA-pipe exponential: it must produce zeros
       const float inv = (l_run > 0.f && q_limit >= 0) ? 1.f / l_run : 0.f;
