@@ -169,7 +169,7 @@ class Attention(nn.Module):
         )
 
 
-def install_into_reference(executor: bool = False) -> None:
+def install_into_reference(executor: bool = False, fuse_qk: bool = False) -> None:
     """Swap this layer into an importable ``minivllm`` (the reference) before models are built.
 
     Every reference model imports the class by name from ``minivllm.models.layers``
@@ -181,6 +181,9 @@ def install_into_reference(executor: bool = False) -> None:
     sizing and the CUDA-Graph capture/replay of the reference's ``InferenceExecutor``
     (``reference_patch.py``); without it only the layer changes and the engine must run with
     ``enforce_eager=True`` (the reference's own capture is broken).
+
+    ``fuse_qk=True`` also rebinds ``QwenAttention.forward`` (models/qwen_base.py:146-190) to the one-kernel
+    q/k RMSNorm + RoPE + cache store (``forward_fused``).
     """
     import importlib
 
@@ -204,3 +207,7 @@ def install_into_reference(executor: bool = False) -> None:
         from . import reference_patch
 
         reference_patch.install_executor()
+    if fuse_qk:
+        from . import reference_patch
+
+        reference_patch.install_fused_qk()

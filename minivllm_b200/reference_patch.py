@@ -15,7 +15,10 @@ and ``Context`` accessors.
 | ``_sample_tokens`` (:776-806), all-greedy batches only | ``ops.greedy_argmax``                         | the full sampling pipeline + multinomial on a one-hot distribution |
 | ``initialize`` (:184-196), ``execute_batch`` (:412-449), TP > 1 only | same + capture on every rank; workers skip logits/sampling | graphs captured on rank 0 only (model_runner.py:113-115); ``ParallelLMHead`` returns ``None`` off rank 0 |
 
-The scheduler, block manager, sequences, models, sampler and ``LLM.generate`` are untouched.
+``install_fused_qk()`` (``install_into_reference(fuse_qk=True)``) additionally rebinds ``QwenAttention.forward``
+(models/qwen_base.py:146-190) to the one-kernel q/k RMSNorm + RoPE + cache store.
+
+The scheduler, block manager, sequences, the rest of the models, the sampler and ``LLM.generate`` are untouched.
 """
 
 from __future__ import annotations
@@ -164,6 +167,55 @@ def install_executor() -> None:
     cls.capture_device_graphs = capture_device_graphs
     cls._execute_with_cuda_graph = _execute_with_cuda_graph
     setattr(cls, _PATCHED, True)
+
+
+def install_fused_qk() -> None:
+    """Rebind ``QwenAttention.forward`` (models/qwen_base.py:146-190, an attention layer of ``minivllm/models``)
+    so that the flat-token path runs ``q_norm / k_norm -> rotary_emb -> store_kv_cache`` as ONE kernel
+    (``Attention.forward_fused`` -> ``mvb200_qk_norm_rope_store``) instead of the ~25
+    elementwise launches of ``RMSNorm.forward`` x 2 (layernorm.py:81-93) and ``RotaryEmbedding.forward``
+    (rotary_embedding.py:166-193).  Same projections, same module attributes, same ``state_dict``; anything the
+    fused kernel does not cover (3-D batches, CPU tensors, a rotary module without cos/sin caches, an ``Attention``
+    that is not ours) takes the reference's own forward."""
+    mod = importlib.import_module("minivllm.models.qwen_base")
+    cls = mod.QwenAttention
+    if getattr(cls, "_mvb200_fused_qk", False):
+        return
+    orig_forward = cls.forward
+
+    def _f32_cache(rot, name):
+        t = getattr(rot, name)
+        if t.dtype == torch.float32:
+            return t
+        # a loader that casts buffers (model.to(bf16)) leaves rounded cos/sin: the reference then rotates with those
+        # values; fp32 copies of them (exact) keep the fused kernel on the same numbers
+        key = "_mvb200_" + name
+        c = getattr(rot, key, None)
+        if c is None or c.device != t.device or c.shape != t.shape:
+            c = t.float()
+            setattr(rot, key, c)
+        return c
+
+    def forward(self, positions, hidden_states):
+        rot = self.rotary_emb
+        if (hidden_states.dim() != 2 or not hidden_states.is_cuda or not hasattr(self.attn, "forward_fused")
+                or not hasattr(rot, "cos_cache") or not hasattr(rot, "sin_cache")
+                or (self.q_norm is None) != (self.k_norm is None)):
+            return orig_forward(self, positions, hidden_states)
+        qkv = self.qkv_proj(hidden_states)
+        n = hidden_states.size(0)
+        q, k, v = qkv.split([self.q_size, self.kv_size, self.kv_size], dim=-1)
+        q = q.view(n, self.num_heads, self.head_dim)
+        k = k.view(n, self.num_kv_heads, self.head_dim)
+        v = v.view(n, self.num_kv_heads, self.head_dim)
+        qw = self.q_norm.weight if self.q_norm is not None else None
+        kw = self.k_norm.weight if self.k_norm is not None else None
+        eps = float(getattr(self.q_norm, "eps", 1e-6)) if self.q_norm is not None else 1e-6
+        o = self.attn.forward_fused(positions, q, k, v, _f32_cache(rot, "cos_cache"), _f32_cache(rot, "sin_cache"), qw, kw, eps)
+        return self.o_proj(o.reshape(n, self.num_heads * self.head_dim))
+
+    cls.forward = forward
+    cls._mvb200_fused_qk = True
 
 
 def hot_graph_sizes(max_batch_size: int) -> list[int]:

@@ -30,7 +30,7 @@ def main() -> None:
         spec["preset"], device=spec.get("device", "cuda"), dtype=spec["dtype"], dropin=spec.get("dropin", True),
         executor=spec.get("executor", False), enforce_eager=not spec.get("graphs", False), calls=calls,
         max_tokens=32, record_logits=True, config_overrides=spec.get("overrides") or {},
-        hide_flash_attn=spec.get("hide_flash_attn"),
+        hide_flash_attn=spec.get("hide_flash_attn"), fuse_qk=spec.get("fuse_qk", False),
         max_num_seqs=8, max_model_len=1024, num_kvcache_blocks=64,
     )
     print("RESULT " + json.dumps(info))

@@ -146,19 +146,24 @@ CASES = [
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode", ["layer_eager", "executor_graphs"])
+@pytest.mark.parametrize("mode", ["layer_eager", "executor_graphs", "executor_graphs_fused_qk"])
 @pytest.mark.parametrize("tag,preset,dtype,overrides,tie_gap", CASES, ids=[c[0] for c in CASES])
 def test_reference_llm_generate_with_b200_layer(cuda_device, tag, preset, dtype, overrides, tie_gap, mode):
     if not _reference_available():
         pytest.fail("oracle/_ref is missing: __graft_entry__.build() must run oracle/make_ref.py before the snapshot")
-    graphs = mode == "executor_graphs"
+    graphs = mode != "layer_eager"
+    fuse_qk = mode.endswith("fused_qk")  # QwenAttention.forward rebound to the one-kernel q/k norm + RoPE + store
+    if fuse_qk and not preset.startswith("qwen"):
+        pytest.skip("the fused q/k path rebinds QwenAttention only")
     info = _run_child({"tag": tag, "preset": preset, "dtype": dtype, "overrides": overrides,
-                       "executor": graphs, "graphs": graphs})
+                       "executor": graphs, "graphs": graphs, "fuse_qk": fuse_qk})
     # the reference's engine really ran our layer and our kernels
     assert info["attention_classes"] == ["minivllm_b200.attention.Attention"], info["attention_classes"]
     seen = set(info["kernels_seen"])
     assert any(k.startswith("decode") for k in seen) and any(k.startswith("prefill") for k in seen) \
-        and any(k.startswith("store") for k in seen), seen
+        and any(k.startswith("store") or k.startswith("qk_norm_rope") for k in seen), seen
+    if fuse_qk:
+        assert any(k.startswith("qk_norm_rope") for k in seen), seen
     if graphs:
         assert info["graphs_captured"] == [1, 2, 4, 8], info["graphs_captured"]
     else:
