@@ -62,8 +62,8 @@ extern "C" int mvb200_prefill_varlen(
   const bool force_generic = getenv("MVB200_PREFILL_GENERIC") != nullptr;
   const bool force_v1 = getenv("MVB200_PREFILL_V1") != nullptr;
   if (!force_generic) {
-    const char* which = getenv("MVB200_PREFILL_KERNEL");
-    int rc = (!force_v1 && which && which[0] == 'd') ? prefill_dbs_dispatch(a, s) : -1;
+    const char* which = getenv("MVB200_PREFILL_KERNEL");  // tuning build: fa2q | dbs (default)
+    int rc = (!force_v1 && !(which && which[0] == 'f')) ? prefill_dbs_dispatch(a, s) : -1;
     if (rc >= 0) return rc;
     rc = force_v1 ? -1 : prefill_fa2q_dispatch(a, s);
     if (rc >= 0) return rc;
@@ -72,12 +72,9 @@ extern "C" int mvb200_prefill_varlen(
   }
 #else
   {
-    // MVB200_PREFILL_KERNEL = dbs | fa2q (A/B of the two tcgen05 kernels while the newer one is being measured)
-    static const bool use_dbs = [] {
-      const char* e = getenv("MVB200_PREFILL_KERNEL");
-      return e ? e[0] == 'd' : false;
-    }();
-    int rc = use_dbs ? prefill_dbs_dispatch(a, s) : -1;
+    // double-buffered-S kernel first (355k vs 389k SM cycles on the cfg3 prefill shape, profiles/r02_prefill_*_run14);
+    // the 128-key-tile kernel covers what it declines
+    int rc = prefill_dbs_dispatch(a, s);
     if (rc >= 0) return rc;
     rc = prefill_fa2q_dispatch(a, s);
     if (rc >= 0) return rc;
