@@ -14,6 +14,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 os.environ["MVB200_LIB"] = os.path.join(ROOT, "minivllm_b200", "libmvb200_trace.so")
+os.environ.setdefault("MVB200_PREFILL_KERNEL", "fa2q")  # the timeline instrumentation lives in the 128-key-tile kernel
 V1 = "--v1" in sys.argv  # trace the one-query-tile kernel instead of the persistent two-tile one
 if V1:
     os.environ["MVB200_PREFILL_V1"] = "1"
