@@ -42,16 +42,13 @@ using pf::fma2;
 using pf::pack2;
 using pf::unpack2;
 
-constexpr int kD = 128;
 constexpr int kBM = 128;                  // rows per query tile
 constexpr int kQTiles = 2;                // query tiles (chains) per work item
 constexpr int kBN = 64;                   // keys per step (= one TMA box = kvcache_block_size granularity)
 constexpr int kStages = 4;                // K ring depth = V ring depth
 constexpr int kThreads = 384;
-constexpr int kQHalfBytes = kBM * 128;    // [128 rows][128 B] = one 64-column half of a Q tile
-constexpr int kQTileBytes = 2 * kQHalfBytes;
+constexpr int kQHalfBytes = kBM * 128;    // [128 rows][128 B] = one 64-column slab of a Q tile (head_dim / 64 slabs)
 constexpr int kKVHalfBytes = kBN * 128;   // [64 keys][128 B]
-constexpr int kKVTileBytes = 2 * kKVHalfBytes;
 constexpr int kTmemCols = 512;
 constexpr int kColS = 0;                  // + t * 128 + buffer * 64
 constexpr int kColO = 256;                // + t * 128
@@ -133,12 +130,16 @@ MVB_DEV Item decode_item(const Params& p, int w) {
   return it;
 }
 
-template <typename T, int kEmu>
+template <typename T, int kEmu, int kD>
 __global__ void __launch_bounds__(kThreads, 1)
 prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
                    const __grid_constant__ CUtensorMap tmap_k,
                    const __grid_constant__ CUtensorMap tmap_v, const Params p) {
+  static_assert(kD == 64 || kD == 128, "head_dim 64 or 128");
   constexpr bool kBf16 = sizeof(T) == 2 && !std::is_same<T, __half>::value;
+  constexpr int kSlabs = kD / 64;                       // 128-byte column slabs per row
+  constexpr int kQTileBytes = kSlabs * kQHalfBytes;
+  constexpr int kKVTileBytes = kSlabs * kKVHalfBytes;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -194,8 +195,9 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
         if (elect_one()) {
           mbar_arrive_expect_tx(bar(BAR_Q_FULL + t), kQTileBytes);
           const uint32_t dst = sQ + t * kQTileBytes;
-          tma_load_3d(dst, &tmap_q, bar(BAR_Q_FULL + t), 0, it.head, it.q0 + it.row0[t]);
-          tma_load_3d(dst + kQHalfBytes, &tmap_q, bar(BAR_Q_FULL + t), 64, it.head, it.q0 + it.row0[t]);
+#pragma unroll
+          for (int h = 0; h < kSlabs; ++h)
+            tma_load_3d(dst + h * kQHalfBytes, &tmap_q, bar(BAR_Q_FULL + t), 64 * h, it.head, it.q0 + it.row0[t]);
         }
         __syncwarp();
       }
@@ -216,12 +218,10 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
         if (elect_one()) {
           mbar_arrive_expect_tx(bar(BAR_K_FULL + s), kKVTileBytes);
           const uint32_t dst = sK + s * kKVTileBytes;
-          if (p.paged) {
-            tma_load_4d(dst, &tmap_k, bar(BAR_K_FULL + s), 0, it.kvh, c_sub, c_blk);
-            tma_load_4d(dst + kKVHalfBytes, &tmap_k, bar(BAR_K_FULL + s), 64, it.kvh, c_sub, c_blk);
-          } else {
-            tma_load_3d(dst, &tmap_k, bar(BAR_K_FULL + s), 0, it.kvh, c_blk);
-            tma_load_3d(dst + kKVHalfBytes, &tmap_k, bar(BAR_K_FULL + s), 64, it.kvh, c_blk);
+#pragma unroll
+          for (int h = 0; h < kSlabs; ++h) {
+            if (p.paged) tma_load_4d(dst + h * kKVHalfBytes, &tmap_k, bar(BAR_K_FULL + s), 64 * h, it.kvh, c_sub, c_blk);
+            else tma_load_3d(dst + h * kKVHalfBytes, &tmap_k, bar(BAR_K_FULL + s), 64 * h, it.kvh, c_blk);
           }
         }
         __syncwarp();
@@ -229,12 +229,10 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
         if (elect_one()) {
           mbar_arrive_expect_tx(bar(BAR_V_FULL + s), kKVTileBytes);
           const uint32_t dst = sV + s * kKVTileBytes;
-          if (p.paged) {
-            tma_load_4d(dst, &tmap_v, bar(BAR_V_FULL + s), 0, it.kvh, c_sub, c_blk);
-            tma_load_4d(dst + kKVHalfBytes, &tmap_v, bar(BAR_V_FULL + s), 64, it.kvh, c_sub, c_blk);
-          } else {
-            tma_load_3d(dst, &tmap_v, bar(BAR_V_FULL + s), 0, it.kvh, c_blk);
-            tma_load_3d(dst + kKVHalfBytes, &tmap_v, bar(BAR_V_FULL + s), 64, it.kvh, c_blk);
+#pragma unroll
+          for (int h = 0; h < kSlabs; ++h) {
+            if (p.paged) tma_load_4d(dst + h * kKVHalfBytes, &tmap_v, bar(BAR_V_FULL + s), 64 * h, it.kvh, c_sub, c_blk);
+            else tma_load_3d(dst + h * kKVHalfBytes, &tmap_v, bar(BAR_V_FULL + s), 64 * h, it.kvh, c_blk);
           }
         }
         __syncwarp();
@@ -258,7 +256,7 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const uint32_t k_lo0 = umma_desc_lo(sK, 16);
     const uint32_t v_lo0 = umma_desc_lo(sV, kKVHalfBytes);  // LBO = distance between the 64-column halves
     const uint32_t s_base = tmem + kColS + t * 128;
-    const uint32_t o_col = tmem + kColO + t * kD;
+    const uint32_t o_col = tmem + kColO + t * 128;
     uint32_t q_uses = 0;
     uint32_t gq = 0;  // Q K^T issued so far (= step index of the next one)
     uint32_t gp = 0;  // P V issued so far
@@ -344,7 +342,7 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
     const int r = quarter * 32 + lane;            // query row within the tile
     const uint32_t lane_base = tmem + ((uint32_t)(quarter * 32) << 16);
     const uint32_t s_col0 = lane_base + kColS + t * 128;
-    const uint32_t o_col = lane_base + kColO + t * kD;
+    const uint32_t o_col = lane_base + kColO + t * 128;
     T* out = reinterpret_cast<T*>(p.out);
     uint32_t g = 0;        // steps consumed by this warpgroup so far (S buffer g & 1; = P V commits it may wait for)
     uint32_t items_done = 0;  // items whose O this warpgroup has written out (phase of BAR_O_FINAL)
@@ -435,7 +433,7 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
             mbar_wait(bar(BAR_V_FULL + st), (cnt / kStages) & 1);
             uint8_t* vg = smem_gen + (sV - smem_base) + st * kKVTileBytes;
             for (int row = start; row < stop; ++row)
-              if (lane < 16)
+              if (lane < 8 * kSlabs)
                 *reinterpret_cast<uint4*>(vg + (lane >> 3) * kKVHalfBytes + row * 128 + (lane & 7) * 16) =
                     make_uint4(0, 0, 0, 0);
             fence_proxy_async_smem();
@@ -510,8 +508,10 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
   if (warp == 0) tmem_dealloc(tmem, kTmemCols);
 }
 
-template <typename T, int kEmu>
+template <typename T, int kEmu, int kD>
 static int launch(const PrefillArgs& a, cudaStream_t stream) {
+  constexpr int kQTileBytes = (kD / 64) * kQHalfBytes;
+  constexpr int kKVTileBytes = (kD / 64) * kKVHalfBytes;
   CUtensorMap mq, mk, mv;
   {
     const uint64_t dims[3] = {(uint64_t)kD, (uint64_t)a.num_heads, (uint64_t)a.total_q};
@@ -560,8 +560,8 @@ static int launch(const PrefillArgs& a, cudaStream_t stream) {
   p.scale_log2 = a.scale * kLog2e;
 
   constexpr int smem = kQTiles * kQTileBytes + 2 * kStages * kKVTileBytes + 8 * BAR_COUNT + 16 + 1024;
-  auto kern = prefill_dbs_kernel<T, kEmu>;
-  static SmemOptIn optin;
+  auto kern = prefill_dbs_kernel<T, kEmu, kD>;
+  static SmemOptIn optin;  // one per instantiation
   if (int rc = optin_dynamic_smem((const void*)kern, smem, &optin, "prefill_dbs")) return rc;
   const int num_sms = device_sm_count();
   const long long items = (long long)p.levels * a.num_seqs * a.num_heads;
@@ -575,7 +575,7 @@ static int launch(const PrefillArgs& a, cudaStream_t stream) {
 // returns -1 when the request is outside what this kernel covers
 int prefill_dbs_dispatch(const PrefillArgs& a, cudaStream_t stream) {
   if (a.dtype != MVB200_BF16 && a.dtype != MVB200_F16) return -1;
-  if (a.head_dim != dbs::kD) return -1;
+  if (a.head_dim != 128 && a.head_dim != 64) return -1;
   if (a.max_seqlen_q <= 0) return -1;
   const long long levels = (a.max_seqlen_q + 255) / 256;
   if (levels > dbs::kMaxLevels || levels * a.num_seqs * a.num_heads >= (1LL << 31)) return -1;
@@ -597,11 +597,14 @@ int prefill_dbs_dispatch(const PrefillArgs& a, cudaStream_t stream) {
     return (v == 0 || v == 8 || v == 16 || v == 24 || v == 32) ? v : dbs::kDefaultEmu;
   }();
 #define MVB_DBS_CASE(E) \
-  if (emu == E) return bf ? dbs::launch<__nv_bfloat16, E>(a, stream) : dbs::launch<__half, E>(a, stream);
+  if (emu == E && a.head_dim == 128) return bf ? dbs::launch<__nv_bfloat16, E, 128>(a, stream) : dbs::launch<__half, E, 128>(a, stream);
   MVB_DBS_CASE(0) MVB_DBS_CASE(8) MVB_DBS_CASE(16) MVB_DBS_CASE(24) MVB_DBS_CASE(32)
 #undef MVB_DBS_CASE
 #endif
-  return bf ? dbs::launch<__nv_bfloat16, dbs::kDefaultEmu>(a, stream) : dbs::launch<__half, dbs::kDefaultEmu>(a, stream);
+  if (a.head_dim == 64)  // GPT-2 / OPT / Qwen2-0.5B heads
+    return bf ? dbs::launch<__nv_bfloat16, dbs::kDefaultEmu, 64>(a, stream) : dbs::launch<__half, dbs::kDefaultEmu, 64>(a, stream);
+  return bf ? dbs::launch<__nv_bfloat16, dbs::kDefaultEmu, 128>(a, stream)
+            : dbs::launch<__half, dbs::kDefaultEmu, 128>(a, stream);
 }
 
 }  // namespace mvb200

@@ -617,10 +617,11 @@ def _oracle_rows(pr, seq, heads, h, kvh, scale):
 
 @pytest.mark.parametrize("bs", [64, 128, 256])
 @pytest.mark.parametrize("dtype", ["bf16", "f16"])
-def test_prefill_tcgen05_ragged_paged(m, cuda_device, bs, dtype):
+@pytest.mark.parametrize("d", [128, 64])
+def test_prefill_tcgen05_ragged_paged(m, cuda_device, bs, dtype, d):
     """Lq/Lk off the 128/64 grid, a fully cached sequence (Lq = 0), single-token suffix,
-    never-written slots full of NaN, block sizes 64/128/256."""
-    h, kvh, d = 8, 2, 128
+    never-written slots full of NaN, block sizes 64/128/256, head_dim 128 and 64 (GPT-2 / OPT heads)."""
+    h, kvh = 8, 2
     lens = [300, 2 * bs, 65, 1000, 129, 64]
     cached = [0, 2 * bs, 64, 3 * bs if 3 * bs < 1000 else bs, 128, 0]
     pr = _paged_prefill_problem(cuda_device, lens, cached, h, kvh, d, bs, TDT[dtype], 21)
@@ -729,9 +730,10 @@ def test_prefill_full_size_against_oracle_samples(m, cuda_device, name, lens, ca
 
 
 def test_prefill_kernel_selection(m, cuda_device):
-    """bf16/fp16 with head_dim 128 -> tcgen05; everything else -> the generic kernel."""
+    """bf16/fp16 with head_dim 128 or 64 -> tcgen05; everything else -> the generic kernel."""
     for dt, d, want in [(torch.bfloat16, 128, "prefill_tcgen05"), (torch.float16, 128, "prefill_tcgen05"),
-                        (torch.float32, 128, "prefill_generic"), (torch.bfloat16, 64, "prefill_generic")]:
+                        (torch.float32, 128, "prefill_generic"), (torch.bfloat16, 64, "prefill_tcgen05"),
+                        (torch.float16, 64, "prefill_tcgen05"), (torch.bfloat16, 96, "prefill_generic")]:
         q = torch.randn(10, 2, d, device=cuda_device).to(dt)
         cu = torch.tensor([0, 10], dtype=torch.int32, device=cuda_device)
         m.prefill_varlen_attention(q, q, q, cu, cu, 10, 10, 0.1)
