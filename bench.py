@@ -717,6 +717,45 @@ def run_prefill(env: Env, args, wl, steps=None) -> dict:
 
 
 # ---------------------------------------------------------------------------
+# N >= 2: one untimed parity check of the cross-process collective that follows the path
+# ---------------------------------------------------------------------------
+
+
+def run_collective_check(env: Env) -> dict:
+    """The fused peer all-reduce + residual add + RMSNorm (``minivllm_b200.comm``, the collective after the
+    row-parallel o_proj / down_proj, linear.py:314-319) across the launcher's ranks, against the CPU oracle (used
+    as the checker, outside every timed region).  Every rank regenerates every rank's input from a shared seed."""
+    torch, dist = env.torch, env.dist
+    from minivllm_b200.comm import PeerAllReduce
+    from oracle import allreduce_oracle as O  # checker only
+
+    world, rank, dev = env.world, env.rank, env.dev
+    gloo = dist.new_group(backend="gloo")
+    shapes = [(8, 2560), (256, 1024), (512, 8192)]  # cfg3 decode message, cfg2 decode message, cfg5 decode message
+    comm = PeerAllReduce(rank, world, max(r * h for r, h in shapes) * 2, group=gloo, device=dev)
+    worst, exact = 0.0, True
+    for rows, hidden in shapes:
+        g = torch.Generator().manual_seed(1000 + rows + hidden)
+        xs = [torch.randn(rows, hidden, generator=g).to(torch.bfloat16) for _ in range(world)]
+        res0 = torch.randn(rows, hidden, generator=g).to(torch.bfloat16)
+        w = (1.0 + 0.1 * torch.randn(hidden, generator=g)).to(torch.bfloat16)
+        want_y, want_res = O.allreduce_add_rms_norm(xs, w, 1e-6, res0)
+        for algo in (1, 2):
+            res = res0.to(dev)
+            y, new_res = comm.allreduce_add_rms_norm(xs[rank].to(dev), w.to(dev), 1e-6, res, algo=algo)
+            torch.cuda.synchronize()
+            exact = exact and bool(torch.equal(new_res.cpu(), want_res))
+            worst = max(worst, (y.cpu().float() - want_y.float()).abs().max().item())
+    t = torch.tensor([worst, 0.0 if exact else 1.0], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dist.barrier()
+    comm.close()
+    return {"kernel": "peer all-reduce + residual add + RMSNorm (one-shot and two-shot, peer stores over NVLink)",
+            "world": world, "shapes": shapes, "max_abs_vs_oracle": float(t[0].item()), "residual_exact": bool(t[1].item() == 0.0),
+            "bar": "residual stream bit-exact for world 2 (<= 1 ulp per hop beyond); normalised output within 0.0625 (bf16)"}
+
+
+# ---------------------------------------------------------------------------
 # leg 3: end-to-end decode tokens/s through the reference's own LLM.generate with the layer swapped in
 # ---------------------------------------------------------------------------
 
@@ -858,6 +897,11 @@ def main():
                 line["gpu_launches"] += p["gpu_launches"]
             except Exception as e:  # noqa: BLE001
                 line["prefill"] = {"error": repr(e)[:300]}
+        if env.world > 1:
+            try:
+                line["collective_check"] = run_collective_check(env)
+            except Exception as e:  # noqa: BLE001
+                line["collective_check"] = {"error": repr(e)[:300]}
         if not args.no_engine:
             # the reference engine's own shutdown tears NCCL state down: last GPU leg
             hard = True
