@@ -275,6 +275,22 @@ MVB200_API int mvb200_peer_allreduce_add_rms_norm(void* const* data_ptrs, void* 
                           int32_t rows, int32_t hidden, float eps, int32_t dtype, int32_t max_ctas,
                           int32_t algo, int32_t gather_residual, void* stream);
 
+/*
+ * The same operator with the NVSwitch doing the sum and the broadcast (NVLS / multimem): two-shot ownership,
+ * multimem.ld_reduce of the owner's rows from a multicast mapping, multimem.st of the finished rows.
+ *   multicast_base / local_base: the multicast mapping and this rank's own mapping of ONE symmetric buffer of
+ *   6 * slot_bytes ([2 parities][X | Y | R][slot_bytes]) that every rank allocated identically (e.g. with
+ *   torch.distributed._symmetric_memory: handle.multicast_ptr / tensor.data_ptr()).
+ *   flag_ptrs / epoch: the flag and epoch buffers of mvb200_peer_allreduce_add_rms_norm (shared with it).
+ * world >= 2; every rank makes the same call.  Replaces linear.py:314-319 + layernorm.py:81-105 like the call above.
+ */
+MVB200_API int mvb200_nvls_allreduce_add_rms_norm(void* multicast_base, void* local_base, int64_t slot_bytes,
+                                       void* const* flag_ptrs, void* epoch, int32_t rank, int32_t world,
+                                       const void* x, int64_t x_row_stride, void* residual,
+                                       int64_t residual_row_stride, const void* weight, void* y,
+                                       int64_t y_row_stride, int32_t rows, int32_t hidden, float eps, int32_t dtype,
+                                       int32_t max_ctas, int32_t gather_residual, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -94,6 +94,12 @@ SIGNATURES = {
          c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
          c_int32, c_int32, c_float, c_int32, c_int32, c_int32, c_int32, c_void_p],
     ),
+    "mvb200_nvls_allreduce_add_rms_norm": (
+        c_int32,
+        [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_int32, c_int32,
+         c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_int64,
+         c_int32, c_int32, c_float, c_int32, c_int32, c_int32, c_void_p],
+    ),
 }
 
 

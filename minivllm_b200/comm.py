@@ -144,3 +144,58 @@ class PeerAllReduce:
 
     def all_reduce(self, x: torch.Tensor, out: torch.Tensor | None = None, algo: int | None = None) -> torch.Tensor:
         return self.allreduce_add_rms_norm(x, None, 0.0, None, out, algo=algo)[0]
+
+
+class NvlsAllReduce(PeerAllReduce):
+    """``PeerAllReduce`` whose large messages go through the NVSwitch (NVLS / multimem): the owner of a row reads
+    it with ``multimem.ld_reduce`` — the switch sums the ranks' copies — and broadcasts the finished row with one
+    ``multimem.st`` (``csrc/peer_allreduce.cu::nvls_allreduce_kernel``).  The symmetric buffer and its multicast
+    mapping come from ``torch.distributed._symmetric_memory`` (plumbing); flags and epochs are the parent's.
+    Needs the default NCCL process group (one process per GPU) and a fabric with multicast support."""
+
+    def __init__(self, rank: int, world: int, max_bytes: int, *, group=None, device=None, max_ctas: int = 0):
+        super().__init__(rank, world, max_bytes, group=group, device=device, max_ctas=max_ctas)
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+
+        if world < 2:
+            raise ValueError("NvlsAllReduce needs at least two ranks")
+        self._sym = symm.empty(6 * self.slot_bytes, dtype=torch.uint8, device=self.device)
+        self._sym.zero_()
+        hdl = symm.rendezvous(self._sym, dist.group.WORLD.group_name)
+        self._sym_handle = hdl
+        self.multicast_ptr = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        if not self.multicast_ptr:
+            raise RuntimeError("this fabric / driver gives no multicast mapping (NVLS unavailable): use PeerAllReduce")
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+
+    #: messages above this size take the NVLS kernel (below it the one-shot peer kernel is latency-optimal)
+    NVLS_MIN_BYTES = 512 * 1024
+
+    def allreduce_add_rms_norm(self, x, weight, eps, residual=None, out=None, *, algo=None, gather_residual=True):
+        """As ``PeerAllReduce.allreduce_add_rms_norm``; ``algo=3`` (or ``None`` for large messages) = NVLS."""
+        nbytes = x.numel() * x.element_size()
+        if algo is None:
+            algo = 3 if nbytes > self.NVLS_MIN_BYTES else 1
+        if algo != 3:
+            return super().allreduce_add_rms_norm(x, weight, eps, residual, out, algo=algo, gather_residual=gather_residual)
+        _require_cuda(x, weight, residual, out)
+        if x.dim() != 2 or x.stride(1) != 1 or not self.fits(x):
+            raise ValueError(f"NVLS all-reduce expects a [rows, hidden] tensor with dense rows that fits the {self.slot_bytes}-byte slots")
+        rows, hidden = x.shape
+        for name, t in (("weight", weight), ("residual", residual), ("out", out)):
+            if t is not None and t.dtype != x.dtype:
+                raise ValueError(f"{name} dtype {t.dtype} != x dtype {x.dtype}")
+        if out is None:
+            out = torch.empty((rows, hidden), dtype=x.dtype, device=x.device)
+        rs = lambda t: t.stride(0) if rows > 1 else hidden  # noqa: E731
+        rc = self._lib.mvb200_nvls_allreduce_add_rms_norm(
+            self.multicast_ptr, self._sym.data_ptr(), self.slot_bytes, self.flag_ptrs, self._epoch, self.rank, self.world,
+            x.data_ptr(), rs(x), residual.data_ptr() if residual is not None else None,
+            rs(residual) if residual is not None else 0, weight.data_ptr() if weight is not None else None,
+            out.data_ptr(), rs(out), rows, hidden, float(eps), _code(x.dtype), self.max_ctas,
+            1 if gather_residual else 0, _stream(),
+        )
+        _native.check(rc, "mvb200_nvls_allreduce_add_rms_norm")
+        return out, residual

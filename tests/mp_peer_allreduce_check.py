@@ -19,7 +19,7 @@ def main():
     import torch.distributed as dist
 
     from harness import fused
-    from minivllm_b200.comm import PeerAllReduce
+    from minivllm_b200.comm import NvlsAllReduce, PeerAllReduce
     from oracle import allreduce_oracle as O
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -30,7 +30,15 @@ def main():
     dist.init_process_group("nccl", device_id=dev)
     gloo = dist.new_group(backend="gloo")
     shapes = [(8, 2560), (1, 3584), (8, 1024), (32, 2560), (64, 2560), (256, 1024), (256, 8192), (512, 8192)]
-    comm = PeerAllReduce(rank, world, max(r * h for r, h in shapes) * 2, group=gloo, device=dev)
+    nvls_note = "ok"
+    try:  # the NVLS (multimem) variant needs a multicast mapping of a symmetric buffer: NVSwitch fabric + driver support
+        comm = NvlsAllReduce(rank, world, max(r * h for r, h in shapes) * 2, group=gloo, device=dev)
+    except Exception as e:  # noqa: BLE001
+        nvls_note = repr(e)[:200]
+        comm = PeerAllReduce(rank, world, max(r * h for r, h in shapes) * 2, group=gloo, device=dev)
+    has_nvls = isinstance(comm, NvlsAllReduce)
+    if rank == 0:
+        print(json.dumps({"nvls": has_nvls, "note": nvls_note}), flush=True)
     ok = True
     for rows, hidden in shapes:
         g = torch.Generator().manual_seed(1000 + rows + hidden)  # same stream on every rank
@@ -41,7 +49,7 @@ def main():
         res = res0.to(dev)
         want_y, want_res = O.allreduce_add_rms_norm(xs, w, 1e-6, res0)
         exact_res, dy = True, 0.0
-        for algo in (1, 2):
+        for algo in (1, 2, 3) if has_nvls else (1, 2):
             res = res0.to(dev)
             y, new_res = comm.allreduce_add_rms_norm(x, wd, 1e-6, res, algo=algo)
             torch.cuda.synchronize()
@@ -79,6 +87,12 @@ def main():
         def run_two_sharded():
             comm.allreduce_add_rms_norm(x, wd, 1e-6, res, out, algo=2, gather_residual=False)
 
+        def run_nvls():
+            comm.allreduce_add_rms_norm(x, wd, 1e-6, res, out, algo=3)
+
+        def run_nvls_sharded():
+            comm.allreduce_add_rms_norm(x, wd, 1e-6, res, out, algo=3, gather_residual=False)
+
         def run_nccl():
             dist.all_reduce(x2)
             fused.add_rms_norm(x2, wd, 1e-6, res2)
@@ -102,6 +116,12 @@ def main():
         t_two_g = timed(g2, 50) / n
         g3, n = graphed(run_two_sharded)
         t_two_sh_g = timed(g3, 50) / n
+        t_nvls_g = t_nvls_sh_g = None
+        if has_nvls:
+            g4, n = graphed(run_nvls)
+            t_nvls_g = round(timed(g4, 50) / n, 2)
+            g5, n = graphed(run_nvls_sharded)
+            t_nvls_sh_g = round(timed(g5, 50) / n, 2)
         good = exact_res and dy <= 0.0625 and d_nccl <= 0.125
         ok = ok and good
         if rank == 0:
@@ -109,7 +129,8 @@ def main():
                               "residual_exact": exact_res, "max_abs_vs_oracle": dy, "max_abs_vs_nccl_path": d_nccl,
                               "us_peer_fused": round(t_peer, 2), "us_nccl_plus_norm": round(t_nccl, 2),
                               "us_peer_fused_graph": round(t_peer_g, 2), "us_nccl_plus_norm_graph": round(t_nccl_g, 2),
-                              "us_twoshot_graph": round(t_two_g, 2), "us_twoshot_sharded_residual_graph": round(t_two_sh_g, 2)}), flush=True)
+                              "us_twoshot_graph": round(t_two_g, 2), "us_twoshot_sharded_residual_graph": round(t_two_sh_g, 2),
+                              "us_nvls_graph": t_nvls_g, "us_nvls_sharded_residual_graph": t_nvls_sh_g}), flush=True)
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
