@@ -750,10 +750,10 @@ def run_collective_check(env: Env) -> dict:
             y, new_res = comm.allreduce_add_rms_norm(xs[rank].to(dev), w.to(dev), 1e-6, res, algo=algo)
             torch.cuda.synchronize()
             worst = max(worst, (y.cpu().float() - want_y.float()).abs().max().item())
-            if algo == 3:  # the switch rounds the fp32 sum its own way (like NCCL's NVLS path): one ulp, elementwise
+            if algo == 3:  # the switch sums and rounds its own way (like NCCL's NVLS path): one ulp of the largest addend
                 a, b = new_res.cpu().float(), want_res.float()
-                ulp = torch.maximum(a.abs(), b.abs()).clamp_min(2.0 ** -126) * 2.0 ** -7
-                nvls_ulps = max(nvls_ulps, ((a - b).abs() / ulp).max().item())
+                big = torch.stack([t_.float().abs() for t_ in xs] + [res0.float().abs()]).max(dim=0).values
+                nvls_ulps = max(nvls_ulps, ((a - b).abs() / (big.clamp_min(2.0 ** -120) * 2.0 ** -7)).max().item())
             else:
                 exact = exact and bool(torch.equal(new_res.cpu(), want_res))
     t = torch.tensor([worst, 0.0 if exact else 1.0, nvls_ulps], device=dev)

@@ -170,14 +170,17 @@ class NvlsAllReduce(PeerAllReduce):
         torch.cuda.synchronize(self.device)
         dist.barrier()
 
-    #: messages above this size take the NVLS kernel (below it the one-shot peer kernel is latency-optimal)
-    NVLS_MIN_BYTES = 512 * 1024
+    #: ``algo=None`` keeps the parent's choice (one-shot / two-shot peer stores): measured on 8 x B200
+    #: (profiles/r02_peer_allreduce_tp8_run21.txt) the NVLS kernel does not beat the two-shot one yet — 8 MiB:
+    #: 69 / 56 us (gathered / sharded residual) against 64 / 52 us; the operator is bound by its four flag
+    #: round trips and the copy in / out of the symmetric buffer, not by NVLink bytes.  Ask for it with ``algo=3``.
+    NVLS_MIN_BYTES = None
 
     def allreduce_add_rms_norm(self, x, weight, eps, residual=None, out=None, *, algo=None, gather_residual=True):
         """As ``PeerAllReduce.allreduce_add_rms_norm``; ``algo=3`` (or ``None`` for large messages) = NVLS."""
         nbytes = x.numel() * x.element_size()
-        if algo is None:
-            algo = 3 if nbytes > self.NVLS_MIN_BYTES else 1
+        if algo is None and self.NVLS_MIN_BYTES is not None and nbytes > self.NVLS_MIN_BYTES:
+            algo = 3
         if algo != 3:
             return super().allreduce_add_rms_norm(x, weight, eps, residual, out, algo=algo, gather_residual=gather_residual)
         _require_cuda(x, weight, residual, out)
