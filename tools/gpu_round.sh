@@ -82,7 +82,7 @@ fi
 if has ncu_prefill; then
   CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --workload cfg3p"
   $CMD > $O/${TAG}_ncu_prefill_plain.log 2>&1 &&
-  $NCU --set full --import-source on -k regex:prefill_fa2q -s 8 -c 2 -f -o $O/${TAG}_prof_prefill $CMD > $O/${TAG}_ncu_prefill.log 2>&1
+  $NCU --set full --import-source on -k regex:prefill_ -s 8 -c 2 -f -o $O/${TAG}_prof_prefill $CMD > $O/${TAG}_ncu_prefill.log 2>&1
   ncu -i $O/${TAG}_prof_prefill.ncu-rep --page raw --csv > $O/${TAG}_prefill_ncu_full.csv 2>/dev/null
 fi
 ls -la $O | tail -40
