@@ -129,7 +129,7 @@ def test_gpu_bf16_token_streams_match_reference(graphs, cuda_device):
     prompts, want = _prompts(g, "tiny-qwen3")
     eng = _engine("tiny-qwen3", cuda_device, torch.bfloat16, enforce_eager=not graphs)
     outs, picked, logits = eng.generate(prompts, 32, forced=want, return_logits=True)
-    assert m.ops.last_kernel() in ("decode_tma_mma", "decode_tma_mma_fused_reduce", "store_vec16", "prefill_tcgen05", "prefill_tcgen05_2q")
+    assert m.ops.last_kernel() in ("decode_tma_mma", "decode_tma_mma_fused_reduce", "store_vec16", "prefill_tcgen05", "prefill_tcgen05_2q", "prefill_tcgen05_dbs")
     _assert_streams(picked, want, logits, margin=0.05, min_exact=0.9)
 
 
