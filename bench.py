@@ -753,6 +753,7 @@ def run_collective_check(env: Env) -> dict:
             if algo == 3:  # the switch sums and rounds its own way (like NCCL's NVLS path): one ulp of the largest addend
                 a, b = new_res.cpu().float(), want_res.float()
                 big = torch.stack([t_.float().abs() for t_ in xs] + [res0.float().abs()]).max(dim=0).values
+                big = torch.maximum(big, b.abs())  # ... or of the sum itself, whichever is larger
                 nvls_ulps = max(nvls_ulps, ((a - b).abs() / (big.clamp_min(2.0 ** -120) * 2.0 ** -7)).max().item())
             else:
                 exact = exact and bool(torch.equal(new_res.cpu(), want_res))
