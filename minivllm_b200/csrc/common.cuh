@@ -7,6 +7,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
 #include "../../include/mvb200.h"
 
@@ -35,6 +36,16 @@ struct SmemOptIn {
 };
 int optin_dynamic_smem(const void* kernel, int bytes, SmemOptIn* cache, const char* what);
 int device_sm_count();  // SMs of the current device (cached per device)
+// A/B knobs (MVB200_DECODE_*, MVB200_ROPE_PAIR, ...) exist in the tuning build only (python minivllm_b200/build.py
+// --trace -> libmvb200_trace.so, selected with MVB200_LIB): the product library carries the measured defaults.
+inline const char* tuning_env(const char* name) {
+#ifdef MVB200_TUNING
+  return getenv(name);
+#else
+  (void)name;
+  return nullptr;
+#endif
+}
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                               cudaStream_t stream, Args&&... args) {

@@ -793,7 +793,7 @@ paged_decode_generic_kernel(const T* __restrict__ q, int64_t q_row_stride,
 static int decode_ctas_per_sm() {
   static int v = 0;
   if (!v) {
-    const char* e = getenv("MVB200_DECODE_CTAS_PER_SM");
+    const char* e = tuning_env("MVB200_DECODE_CTAS_PER_SM");
     v = e ? atoi(e) : 2;
     if (v < 1) v = 1;
     if (v > 2) v = 2;
@@ -805,7 +805,7 @@ static int decode_ctas_per_sm() {
 // or with decode_reduce_kernel launched behind it (PDL).
 static bool decode_fused_reduce() {
   static const bool v = [] {
-    const char* e = getenv("MVB200_DECODE_REDUCE");
+    const char* e = tuning_env("MVB200_DECODE_REDUCE");
     return !(e && e[0] == 'k');
   }();
   return v;
@@ -839,7 +839,7 @@ static int launch_fast(DecodeParams& p, const void* k_cache, const void* v_cache
   const bool fused = p.num_splits > 1 && decode_fused_reduce();
   if (p.num_splits > 1 && !fused) p.tickets = nullptr;
   // one unit per CTA: nothing to balance, skip the counter round trips
-  if (!fused && p.total_units <= ctas && getenv("MVB200_DECODE_DYNAMIC") == nullptr) p.sched = nullptr;
+  if (!fused && p.total_units <= ctas && tuning_env("MVB200_DECODE_DYNAMIC") == nullptr) p.sched = nullptr;
   cudaError_t le = launch_pdl(kern, dim3((unsigned)ctas), dim3(kDecodeThreads), (size_t)smem, stream, mk, mv, p);
   if (le != cudaSuccess)
     return fail(MVB200_ECUDA, "paged_decode_kernel: %s", cudaGetErrorString(le));
@@ -869,7 +869,7 @@ static int launch_generic(const void* q, int64_t q_row_stride, const void* k_cac
 static int decode_stages() {
   static int v = 0;
   if (!v) {
-    const char* e = getenv("MVB200_DECODE_STAGES");
+    const char* e = tuning_env("MVB200_DECODE_STAGES");
     v = e ? atoi(e) : 3;
     if (v < 2) v = 2;
     if (v > 6) v = 6;
@@ -917,7 +917,7 @@ extern "C" int32_t mvb200_decode_suggest_splits(int32_t batch, int32_t num_kv_he
   const int64_t slots = 2LL * sm_count;
   int64_t s = units >= sm_count ? 1 : slots / units;  // never more units than resident CTA slots: one wave
   static const int env_cap = [] {
-    const char* e = getenv("MVB200_DECODE_MAX_SPLITS");
+    const char* e = mvb200::tuning_env("MVB200_DECODE_MAX_SPLITS");
     return e ? atoi(e) : 0;
   }();
   const int max_by_work = tiles / 4 > 0 ? tiles / 4 : 1;
@@ -960,7 +960,7 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
                          ((uintptr_t)store->key % 16 == 0) && ((uintptr_t)store->value % 16 == 0) &&
                          store->key_row_stride % 8 == 0 && store->value_row_stride % 8 == 0 &&
                          ((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) && ((uintptr_t)q % 4 == 0) &&
-                         (q_row_stride % 2 == 0) && num_blocks < (1LL << 31) && getenv("MVB200_DECODE_NO_FUSED_STORE") == nullptr;
+                         (q_row_stride % 2 == 0) && num_blocks < (1LL << 31) && tuning_env("MVB200_DECODE_NO_FUSED_STORE") == nullptr;
     if (!fusable) {
       const int rc = mvb200_store_kvcache(store->key, store->value, store->key_row_stride, store->value_row_stride,
                                           (void*)k_cache, (void*)v_cache, store->slot_mapping, batch,
@@ -1044,7 +1044,7 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
     if (units * num_splits >= (1LL << 31)) return fail(MVB200_EINVAL, "paged_decode: too many work units");
     p.total_units = (int32_t)(units * num_splits);
     p.q_bulk = (((uintptr_t)q & 15) == 0 && (q_row_stride % 8) == 0) ? 1 : 0;
-    static const bool no_early = getenv("MVB200_DECODE_NO_EARLY") != nullptr;
+    static const bool no_early = tuning_env("MVB200_DECODE_NO_EARLY") != nullptr;
     // run-ahead pays where start-up latency shows: at most one unit per resident CTA (measured, run 7: with
     // several units per CTA — 512 x 1024-token sequences on one kv head — it costs 7 us per launch)
     // ... and never together with the fused store (whose source rows the preceding kernels produce; measured,

@@ -375,7 +375,7 @@ extern "C" int mvb200_qk_norm_rope_store(
   note_kernel("qk_norm_rope_store");
   cudaStream_t s = (cudaStream_t)stream;
   // 128-bit path: 16-bit elements, head_dim 128, every row start 16-byte aligned
-  bool vec_ok = eb == 2 && head_dim == 128 && getenv("MVB200_ROPE_PAIR") == nullptr;
+  bool vec_ok = eb == 2 && head_dim == 128 && tuning_env("MVB200_ROPE_PAIR") == nullptr;
   for (int64_t st : strides) vec_ok = vec_ok && (st % 8 == 0);
   for (const void* ptr : ptrs) vec_ok = vec_ok && (reinterpret_cast<uintptr_t>(ptr) % 16 == 0);
   vec_ok = vec_ok && ((reinterpret_cast<uintptr_t>(cos_cache) | reinterpret_cast<uintptr_t>(sin_cache)) % 16 == 0);

@@ -40,7 +40,8 @@ fi
 if has decode_sweep; then
   : > $O/${TAG}_decode_sweep.jsonl
   sw() { label=$1; wl=$2; shift 2
-    env "$@" timeout 300 python bench.py --no-cpu-baseline --steps 20 --warmup 3 --workload $wl ${EXTRA:-} 2>>$O/${TAG}_sweep.err | python tools/bench_line.py $label >> $O/${TAG}_decode_sweep.jsonl
+    # the MVB200_DECODE_* knobs exist in the tuning build only (python minivllm_b200/build.py --trace)
+    env "$@" MVB200_LIB=minivllm_b200/libmvb200_trace.so timeout 300 python bench.py --no-cpu-baseline --steps 20 --warmup 3 --workload $wl ${EXTRA:-} 2>>$O/${TAG}_sweep.err | python tools/bench_line.py $label >> $O/${TAG}_decode_sweep.jsonl
   }
   sw cfg4_default cfg4 A=1
   sw cfg4_noearly cfg4 MVB200_DECODE_NO_EARLY=1
