@@ -63,6 +63,19 @@ def test_argument_errors_are_reported_without_a_gpu(native):
     rc = lib.mvb200_paged_decode(None, 0, None, None, None, 0, None, None, 0, None, 0,
                                  2, 7, 2, 128, 64, 10, 4, 1, 1.0, 2, None)
     assert rc == 1 and "multiple" in native.last_error()
+    # the _ex entry with a fused store whose pointers are missing
+    store = native.DecodeStore(None, None, 0, 0, None)
+    rc = lib.mvb200_paged_decode_ex(ctypes.c_void_p(16), 256, ctypes.c_void_p(16), ctypes.c_void_p(16), ctypes.c_void_p(16), 4,
+                                    ctypes.c_void_p(16), ctypes.c_void_p(16), 256, None, 0, 2, 2, 2, 128, 64, 10, 4, 1, 1.0, 2, 0,
+                                    ctypes.byref(store), None)
+    assert rc == 1 and "fused store" in native.last_error()
+    # NVLS all-reduce: world of one, null buffers, unaligned slot
+    rc = lib.mvb200_nvls_allreduce_add_rms_norm(None, None, 1024, None, None, 0, 1, None, 0, None, 0, None, None, 0,
+                                                4, 256, 1e-6, 2, 0, 1, None)
+    assert rc == 1 and "rank/world" in native.last_error()
+    rc = lib.mvb200_nvls_allreduce_add_rms_norm(None, None, 1 << 20, None, None, 0, 2, None, 0, None, 0, None, None, 0,
+                                                4, 256, 1e-6, 2, 0, 1, None)
+    assert rc == 1 and "null" in native.last_error()
     with pytest.raises(ValueError):
         native.check(1, "x")
     with pytest.raises(RuntimeError):

@@ -738,3 +738,32 @@ def test_prefill_kernel_selection(m, cuda_device):
         cu = torch.tensor([0, 10], dtype=torch.int32, device=cuda_device)
         m.prefill_varlen_attention(q, q, q, cu, cu, 10, 10, 0.1)
         assert m.ops.last_kernel().startswith(want)
+
+
+def test_second_device_in_one_process(m, cuda_device):
+    """One process driving two GPUs (a single-process multi-GPU harness): the per-device caches of the library
+    (dynamic shared-memory opt-in, SM count) must not carry over from the first device — the decode and prefill
+    kernels launched on cuda:1 after cuda:0 give the same results as on cuda:0."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible GPUs")
+    d, bs, kvh, g = 128, 64, 2, 4
+    h = kvh * g
+    ctxs = [300, 65, 1000]
+    outs = []
+    for dev in (torch.device("cuda", 0), torch.device("cuda", 1)):
+        with torch.cuda.device(dev):
+            kc, vc, bt, cl = _random_paged(dev, len(ctxs), ctxs, kvh, d, bs, torch.bfloat16, 5)
+            gen = torch.Generator().manual_seed(3)
+            kc.copy_(torch.randn(kc.shape, generator=gen).to(torch.bfloat16))
+            vc.copy_(torch.randn(vc.shape, generator=gen).to(torch.bfloat16))
+            q = torch.randn(len(ctxs), h, d, generator=gen).to(torch.bfloat16).to(dev)
+            dec = m.paged_decode_attention(q, kc, vc, bt, cl, d**-0.5, num_splits=3)
+            n = sum(ctxs)
+            qp = torch.randn(n, h, d, generator=gen).to(torch.bfloat16).to(dev)
+            kp = torch.randn(n, kvh, d, generator=gen).to(torch.bfloat16).to(dev)
+            cu = torch.tensor(np.concatenate([[0], np.cumsum(ctxs)]).astype(np.int32), device=dev)
+            pre = m.prefill_varlen_attention(qp, kp, kp, cu, cu, max(ctxs), max(ctxs), d**-0.5)
+            assert m.ops.last_kernel().startswith("prefill_tcgen05")
+            torch.cuda.synchronize(dev)
+            outs.append((dec.cpu(), pre.cpu()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
