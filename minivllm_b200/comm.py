@@ -171,7 +171,7 @@ class NvlsAllReduce(PeerAllReduce):
         dist.barrier()
 
     #: ``algo=None`` keeps the parent's choice (one-shot / two-shot peer stores): measured on 8 x B200
-    #: (profiles/r02_peer_allreduce_tp8_run21.txt) the NVLS kernel does not beat the two-shot one yet — 8 MiB:
+    #: (profiles/r02_peer_allreduce_tp8_run26.txt) the NVLS kernel does not beat the two-shot one yet — 8 MiB:
     #: 69 / 56 us (gathered / sharded residual) against 64 / 52 us; the operator is bound by its four flag
     #: round trips and the copy in / out of the symmetric buffer, not by NVLink bytes.  Ask for it with ``algo=3``.
     NVLS_MIN_BYTES = None
