@@ -803,6 +803,7 @@ def run_engine(env: Env | None, args, wl) -> dict:
     warm, real = engine_prompts(wl, vocab)
     info = ref_engine.run(
         wl["preset"], device="cuda", dtype="bfloat16", dropin=True, executor=True, fuse_qk=True, enforce_eager=False, fast_init=True,
+        peer_allreduce=world > 1 and os.environ.get("MVB200_ENGINE_NCCL") is None,
         calls=[warm, real], max_tokens=[1, wl["new_tokens"]], tensor_parallel_size=world, under_torchrun=world > 1,
         **engine_config(wl))
     if info.get("worker"):
@@ -811,7 +812,8 @@ def run_engine(env: Env | None, args, wl) -> dict:
     return {
         "metric": "end-to-end decode tokens/s", "value": c["decode_tokens"] / c["decode_s"], "unit": "tokens/s",
         "n_gpus": world, "parallelism": f"tp{world}", "dtype": "bf16", "data": "synthetic prompts, random-init weights",
-        "engine": "the reference's own minivllm.LLM.generate (oracle/_ref, unmodified) with minivllm_b200.install_into_reference(executor=True, fuse_qk=True)",
+        "engine": "the reference's own minivllm.LLM.generate (oracle/_ref, unmodified) with minivllm_b200.install_into_reference(executor=True, fuse_qk=True"
+                  + (", peer_allreduce=True)" if world > 1 and os.environ.get("MVB200_ENGINE_NCCL") is None else ")"),
         "config": {"workload": wl["name"], "model": wl["preset"], "sequences": wl["seqs"], "prompt_tokens": wl["prompt"],
                    "prefix_cached_tokens": wl["cached"], "new_tokens": wl["new_tokens"], "cuda_graph": True},
         "decode_ms_per_step": c["decode_s"] / max(c["decode_steps"], 1) * 1e3, "decode_steps": c["decode_steps"],

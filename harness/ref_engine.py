@@ -55,6 +55,7 @@ def run(
     isolate_cuda: bool = True,
     profile: str = "",
     fuse_qk: bool = False,
+    peer_allreduce: bool = False,
     **config_kw,
 ) -> dict:
     """Build one reference ``LLM`` and run ``generate`` once per entry of ``calls`` (later calls can hit the
@@ -73,7 +74,7 @@ def run(
     if dropin:
         import minivllm_b200
 
-        minivllm_b200.install_into_reference(executor=executor, fuse_qk=fuse_qk)
+        minivllm_b200.install_into_reference(executor=executor, fuse_qk=fuse_qk, peer_allreduce=peer_allreduce)
         info["native_lib"] = minivllm_b200._native.LIB_PATH
     elif executor:  # executor subsystems only, the reference's own attention layer (CPU-testable)
         from minivllm_b200 import reference_patch

@@ -169,7 +169,7 @@ class Attention(nn.Module):
         )
 
 
-def install_into_reference(executor: bool = False, fuse_qk: bool = False) -> None:
+def install_into_reference(executor: bool = False, fuse_qk: bool = False, peer_allreduce: bool = False) -> None:
     """Swap this layer into an importable ``minivllm`` (the reference) before models are built.
 
     Every reference model imports the class by name from ``minivllm.models.layers``
@@ -184,6 +184,8 @@ def install_into_reference(executor: bool = False, fuse_qk: bool = False) -> Non
 
     ``fuse_qk=True`` also rebinds ``QwenAttention.forward`` (models/qwen_base.py:146-190) to the one-kernel
     q/k RMSNorm + RoPE + cache store (``forward_fused``).
+    ``peer_allreduce=True`` rebinds ``RowParallelLinear.forward`` (linear.py:314-319): decode-size all-reduces go
+    through the one-shot NVLink peer kernel, everything else stays on NCCL.
     """
     import importlib
 
@@ -211,3 +213,7 @@ def install_into_reference(executor: bool = False, fuse_qk: bool = False) -> Non
         from . import reference_patch
 
         reference_patch.install_fused_qk()
+    if peer_allreduce:
+        from . import reference_patch
+
+        reference_patch.install_peer_allreduce()
