@@ -1047,10 +1047,13 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
     static const bool no_early = tuning_env("MVB200_DECODE_NO_EARLY") != nullptr;
     // run-ahead pays where start-up latency shows: at most one unit per resident CTA (measured, run 7: with
     // several units per CTA — 512 x 1024-token sequences on one kv head — it costs 7 us per launch)
-    // ... and never together with the fused store (whose source rows the preceding kernels produce; measured,
-    // run 8: the one-launch step is fastest without it)
-    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early && store == nullptr &&
+    // The fused store does not stand in the way: the new rows are read by a CONSUMER warp, after its own dependency
+    // wait (runs 31/32: one-launch step of the small shapes -7 ... -11 %).
+    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early &&
                p.total_units <= (int64_t)decode_ctas_per_sm() * device_sm_count()) ? 1 : 0;
+    // a run-ahead producer would queue the unit's Q copy behind the tiles it fetched early: the consumers (which wait
+    // for the preceding kernel at the top) read their Q fragments from global memory instead
+    if (p.early && tuning_env("MVB200_DECODE_EARLY_QBULK") == nullptr) p.q_bulk = 0;
     p.new_k = store ? store->key : nullptr;
     p.new_v = store ? store->value : nullptr;
     p.new_k_stride = store ? store->key_row_stride : 0;
