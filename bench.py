@@ -409,7 +409,7 @@ def run_reference_arm(args, wl):
         "e2e": {"value": base["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ---------------------------------------------------------------------------
@@ -861,7 +861,19 @@ def finish(env: Env | None, hard_exit: bool):
             env.dist.destroy_process_group()
 
 
+_STDOUT = sys.stdout
+
+
+def emit(line: dict) -> None:
+    """The ONE JSON line of a run, on the process's real stdout (everything else — the reference's loggers included —
+    goes to stderr, see main)."""
+    _STDOUT.write(json.dumps(line) + "\n")
+    _STDOUT.flush()
+
+
 def main():
+    # the reference configures loggers that write to sys.stdout when it is imported: keep stdout for the JSON line
+    sys.stdout = sys.stderr
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -889,7 +901,7 @@ def main():
         env = Env() if int(os.environ.get("WORLD_SIZE", "1")) > 1 else None
         line = run_engine(env, args, wl)
         if not line.get("worker") and int(os.environ.get("RANK", "0")) == 0:
-            print(json.dumps(line), flush=True)
+            emit(line)
         finish(env, hard_exit=True)
         return
     env = Env()
@@ -899,7 +911,7 @@ def main():
             base = run_prefill_cpu_baseline(wl, steps=3, warmup=1)
             line["cpu_baseline"] = {k_: base[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
         if env.rank == 0:
-            print(json.dumps(line), flush=True)
+            emit(line)
         finish(env, hard_exit=False)
         return
     line = run_decode(env, args, wl, wl_key)
@@ -935,7 +947,7 @@ def main():
         base = run_cpu_baseline(wl, steps=10, warmup=1)
         line["cpu_baseline"] = {k_: base[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
     if env.rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     finish(env, hard_exit=hard)
 
 
