@@ -42,6 +42,19 @@ __device__ __forceinline__ void body(float (&a)[2 * OPS], float s, float m) {
       uint32_t r = __float_as_uint(x), q = __float_as_uint(y);
       asm volatile("mad.lo.u32 %0, %1, 8388608, %0;" : "+r"(r) : "r"(q));
       x = __uint_as_float(r);
+    } else if (kOp == 11) {  // the softmax inner step of one score pair: FFMA2, 2 x MUFU.EX2, FADD2, F2FP
+      uint32_t r;
+      asm volatile("{.reg .b64 t, u, v, w; .reg .f32 a, b; mov.b64 t, {%0,%1}; mov.b64 u, {%3,%3}; mov.b64 v, {%4,%4};"
+                   " fma.rn.f32x2 t, t, u, v; mov.b64 {a,b}, t; ex2.approx.ftz.f32 a, a; ex2.approx.ftz.f32 b, b;"
+                   " mov.b64 w, {a,b}; add.rn.f32x2 t, t, w; cvt.rn.bf16x2.f32 %2, b, a; mov.b64 {%0,%1}, t;}"
+                   : "+f"(x), "+f"(y), "=r"(r) : "f"(s), "f"(m));
+      y += __uint_as_float(r & 0x7f800000u) * 0.f;
+    } else if (kOp == 12) {  // same without the exponentials (FMA + ALU pipes only)
+      uint32_t r;
+      asm volatile("{.reg .b64 t, u, v; mov.b64 t, {%0,%1}; mov.b64 u, {%3,%3}; mov.b64 v, {%4,%4};"
+                   " fma.rn.f32x2 t, t, u, v; add.rn.f32x2 t, t, v; cvt.rn.bf16x2.f32 %2, %1, %0; mov.b64 {%0,%1}, t;}"
+                   : "+f"(x), "+f"(y), "=r"(r) : "f"(s), "f"(m));
+      y += __uint_as_float(r & 0x7f800000u) * 0.f;
     } else if (kOp == 10) {  // FMUL2
       asm volatile("{.reg .b64 t, u; mov.b64 t, {%0,%1}; mov.b64 u, {%2,%2}; mul.rn.f32x2 t, t, u; mov.b64 {%0,%1}, t;}"
                    : "+f"(x), "+f"(y) : "f"(s));
@@ -101,6 +114,9 @@ int main() {
   run<6>("F2FP.BF16.PACK_AB", 1, out, cyc);
   run<7>("FMNMX3", 1, out, cyc);
   run<9>("IMAD (x * 2^23 + y)", 1, out, cyc);
+  printf("mixes: cycles per score PAIR (FFMA2 + 2 MUFU + FADD2 + F2FP [+1 FFMA]); alone these cost 3 x 2.1 + 2 x 8\n");
+  run<11>("softmax pair step (all pipes)", 1, out, cyc);
+  run<12>("softmax pair step without MUFU", 1, out, cyc);
   cudaError_t e = cudaGetLastError();
   printf("status: %s\n", cudaGetErrorString(e));
   return e != cudaSuccess;
