@@ -369,33 +369,29 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
       const int q_limit = it.shift + row0_t + r;  // largest key index this row may see
       float m_ref = -INFINITY, l_run = 0.f;
 
-      // Software pipeline over the steps: the scores of step j+1 (ready early, S is double-buffered) are fetched,
-      // masked and max-reduced WHILE the exponentials of step j are issued, so that the tcgen05.ld latency and the
-      // dependent max chain of a step never sit between two exponential phases of this lone warp.
-      auto load_scores = [&](uint32_t gstep, int jj, float (&dst)[kBN]) {
-        const uint32_t b = gstep & 1;
-        mbar_wait(bar(BAR_S_FULL + t * 2 + b), (gstep >> 1) & 1);
+      for (int j = 0; j < n_t; ++j, ++g) {
+        const uint32_t buf = g & 1;
+        const uint32_t s_col = s_col0 + buf * kBN;
+        mbar_wait(bar(BAR_S_FULL + t * 2 + buf), (g >> 1) & 1);
         tc_fence_after();
-        uint32_t raw[2][32];
-        tmem_ld32(s_col0 + b * kBN, raw[0]);
-        tmem_ld32(s_col0 + b * kBN + 32, raw[1]);
-        tmem_wait_ld();
+        float s[kBN];
+        {
+          uint32_t raw[2][32];
+          tmem_ld32(s_col, raw[0]);
+          tmem_ld32(s_col + 32, raw[1]);
+          tmem_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          dst[i] = __uint_as_float(raw[0][i]);
-          dst[32 + i] = __uint_as_float(raw[1][i]);
+          for (int i = 0; i < 32; ++i) {
+            s[i] = __uint_as_float(raw[0][i]);
+            s[32 + i] = __uint_as_float(raw[1][i]);
+          }
         }
-        const int c0 = jj * kBN;
-        if (c0 + kBN - 1 > it.shift + row0_t) {  // step touches the diagonal / the end (uniform test)
-          const int lim = q_limit - c0;
+        const int col0 = j * kBN;
+        if (col0 + kBN - 1 > it.shift + row0_t) {  // step touches the diagonal / the end (uniform test)
+          const int lim = q_limit - col0;
 #pragma unroll
-          for (int i = 0; i < kBN; ++i) dst[i] = i <= lim ? dst[i] : -INFINITY;
+          for (int i = 0; i < kBN; ++i) s[i] = i <= lim ? s[i] : -INFINITY;
         }
-      };
-      float s[kBN];
-      load_scores(g, 0, s);
-      float mx_raw;
-      {
         float mx4[4];  // four independent chains of 3-input max
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4) {
@@ -403,14 +399,7 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
 #pragma unroll
           for (int i = 2; i < 16; i += 2) mx4[q4] = fmaxf(mx4[q4], fmaxf(s[16 * q4 + i], s[16 * q4 + i + 1]));
         }
-        mx_raw = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      }
-
-      for (int j = 0; j < n_t; ++j, ++g) {
-        const uint32_t buf = g & 1;
-        const uint32_t s_col = s_col0 + buf * kBN;
-        const int col0 = j * kBN;
-        const float mx = mx_raw * p.scale_log2;
+        const float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * p.scale_log2;
         // lazy rescale: keep exponentiating against m_ref until the true max outruns it by 2^8
         const bool grow = mx > m_ref + kRescaleThreshold;
         if (__any_sync(0xffffffffu, grow)) {
@@ -454,26 +443,8 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
         const uint64_t scale2 = pack2(p.scale_log2, p.scale_log2);
         const uint64_t negm2 = pack2(-m_use, -m_use);
         uint64_t sum2[2] = {pack2(0.f, 0.f), pack2(0.f, 0.f)};  // two chains: FADD2 latency off the critical path
-        float s_nxt[kBN];
-        const bool has_next = j + 1 < n_t;
-        if (has_next) {
-          load_scores(g + 1, j + 1, s_nxt);
-        } else {
-#pragma unroll
-          for (int i = 0; i < kBN; ++i) s_nxt[i] = -INFINITY;
-        }
-        float nmx4[4];
 #pragma unroll
         for (int chunk = 0; chunk < kBN / 32; ++chunk) {
-          // the next step's row maximum, two chains per chunk, between this chunk's exponentials
-#pragma unroll
-          for (int q2 = 0; q2 < 2; ++q2) {
-            const int o = chunk * 32 + q2 * 16;
-            float v = fmaxf(s_nxt[o], s_nxt[o + 1]);
-#pragma unroll
-            for (int i = 2; i < 16; i += 2) v = fmaxf(v, fmaxf(s_nxt[o + i], s_nxt[o + i + 1]));
-            nmx4[chunk * 2 + q2] = v;
-          }
           uint32_t pk[16];
 #pragma unroll
           for (int i = 0; i < 32; i += 2) {
@@ -501,9 +472,6 @@ prefill_dbs_kernel(const __grid_constant__ CUtensorMap tmap_q,
         float sum_lo, sum_hi;
         unpack2(add2(sum2[0], sum2[1]), sum_lo, sum_hi);
         l_run += sum_lo + sum_hi;
-        mx_raw = fmaxf(fmaxf(nmx4[0], nmx4[1]), fmaxf(nmx4[2], nmx4[3]));
-#pragma unroll
-        for (int i = 0; i < kBN; ++i) s[i] = s_nxt[i];
       }
 
       // ---- epilogue: O / l -> global ----
