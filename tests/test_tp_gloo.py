@@ -116,7 +116,15 @@ def _ref_engine_worker(rank: int, world: int, port: int, prompts, ret):
     torch.set_num_threads(2)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     from harness import ref_engine
+    from oracle import reference_engine as R
 
+    # the optional rebindings must leave everything they do not cover on the reference's own path: on CPU tensors
+    # QwenAttention.forward and RowParallelLinear.forward (dist.all_reduce over gloo) stay the reference's
+    R.import_reference("cpu", hide_flash_attn=True, isolate_cuda=True)
+    from minivllm_b200 import reference_patch
+
+    reference_patch.install_fused_qk()
+    reference_patch.install_peer_allreduce()
     info = ref_engine.run("tiny-qwen3", device="cpu", dtype="float32", executor=True, calls=[prompts], max_tokens=16,
                           tensor_parallel_size=world, under_torchrun=True, max_num_seqs=8, max_model_len=1024,
                           num_kvcache_blocks=64)
