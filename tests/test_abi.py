@@ -52,6 +52,12 @@ def test_host_side_helpers_need_no_gpu(native):
     s = lib.mvb200_decode_suggest_splits(1, 4, 32768, 148)
     assert 32 <= s <= 128
     assert lib.mvb200_decode_suggest_splits(1, 1, 64, 148) == 1
+    # never more units than resident CTA slots (2 per SM): one wave, the fused reduction waits for nobody queued
+    for batch, kvh, ctx in ((8, 8, 2304), (1, 4, 32768), (16, 2, 4096), (3, 1, 100000), (100, 1, 8192)):
+        s = lib.mvb200_decode_suggest_splits(batch, kvh, ctx, 148)
+        assert 1 <= s <= 128 and batch * kvh * s <= 2 * 148, (batch, kvh, ctx, s)
+    assert lib.mvb200_decode_suggest_splits(8, 8, 2304, 148) == 4
+    assert lib.mvb200_decode_suggest_splits(512, 1, 1024, 148) == 1  # splitting a multi-wave batch costs more than its tail
 
 
 def test_argument_errors_are_reported_without_a_gpu(native):
