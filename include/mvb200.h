@@ -234,6 +234,37 @@ MVB200_API int mvb200_greedy_argmax(const void* logits, int64_t row_stride, int3
                           int64_t* out_index, float* out_value, int64_t index_offset, void* stream);
 
 /*
+ * greedy_argmax_static — mvb200_greedy_argmax for callers that have no scratch to give and may not allocate.
+ * No counterpart in the reference (its sampler runs on torch tensors and torch's allocator); it exists for
+ * hosts of this library that cannot obtain device memory at call time: a serving process that handed every
+ * spare byte of HBM to the KV cache when it started, a binding from another language (cgo / JNI / a bare
+ * ctypes shim) that carries no device allocator of its own, or a step loop that cannot afford the
+ * device-wide stall a cudaMalloc brings.  Same arguments and same result as mvb200_greedy_argmax minus the
+ * workspace pair; logits, out_index and out_value are still the caller's.
+ *
+ * The per-chunk partial winners go to an array compiled into the library (MVB200_GREEDY_ARGMAX_STATIC_BYTES,
+ * 256-byte aligned).  Each GPU that loads libmvb200.so holds that much memory until the process exits.  The
+ * call never runs cudaMalloc, cudaFree or any allocating routine.
+ *   limit     : when the vocabulary is cut into more than one chunk per row, the rows x chunks partial keys
+ *               (mvb200_greedy_argmax_workspace_bytes(rows, vocab)) must fit MVB200_GREEDY_ARGMAX_STATIC_BYTES,
+ *               otherwise MVB200_EINVAL with both sizes in the message.  The present chunking never asks for
+ *               more than 590 keys = 4720 bytes (rows = 295), and from 296 rows on uses one chunk and no
+ *               scratch, so every rows x vocab is accepted today; the check keeps a later change of the
+ *               chunking from writing past the array.
+ *   first call: the first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *               with the caller's current device — make the device that owns `stream` current).  Make that
+ *               first call outside any stream capture.
+ *   sharing   : all calls on a device use the same array and it keeps whatever the last call wrote.  Nothing
+ *               in it has to start at zero — the first pass rewrites every key the second pass reads — but
+ *               two calls that overlap on the GPU (different streams, or graph branches running side by side)
+ *               race on it and can return each other's winners.  Keep calls on one device ordered.
+ */
+#define MVB200_GREEDY_ARGMAX_STATIC_BYTES 8192
+MVB200_API int mvb200_greedy_argmax_static(const void* logits, int64_t row_stride, int32_t rows, int32_t vocab,
+                          int32_t dtype, int64_t* out_index, float* out_value, int64_t index_offset,
+                          void* stream);
+
+/*
  * Peer all-reduce fused with residual add + RMSNorm.
  * Replaces, for decode-size messages, dist.all_reduce in RowParallelLinear.forward
  * (models/layers/linear.py:314-319) and the RMSNorm.forward(x, residual) that follows it

@@ -80,6 +80,10 @@ SIGNATURES = {
         [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_size_t,
          c_void_p, c_void_p, c_int64, c_void_p],
     ),
+    "mvb200_greedy_argmax_static": (
+        c_int32,
+        [c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p, c_int64, c_void_p],
+    ),
     "mvb200_peer_flag_bytes": (c_int32, []),
     "mvb200_peer_epoch_bytes": (c_int32, []),
     "mvb200_peer_max_ctas": (c_int32, []),

@@ -17,6 +17,8 @@
 // one CTA per (row, vocabulary chunk) with 16-byte loads, a second tiny pass when chunks > 1.
 #include <math.h>
 
+#include <mutex>
+
 #include "common.cuh"
 
 namespace mvb200 {
@@ -299,5 +301,82 @@ extern "C" int mvb200_greedy_argmax(const void* logits, int64_t row_stride, int3
       return launch_argmax<float>(logits, row_stride, rows, vocab, workspace, out_index, out_value, index_offset, s);
     default:
       return fail(MVB200_EINVAL, "greedy_argmax: unknown dtype %d", dtype);
+  }
+}
+
+// ---- greedy argmax without a caller workspace -------------------------------------------------------
+// Some hosts of this library cannot hand us scratch memory and must not have us allocate any: a serving
+// process that gave all spare HBM to the KV cache at start-up, a host-language binding (cgo / JNI / ctypes shim)
+// that owns no device allocator, or a step loop where cudaMalloc's implicit device synchronisation is not
+// acceptable.  For them the per-chunk winners of the two-pass argmax live in the array below, which is part of
+// the library image: every GPU that loads libmvb200.so carries these 8 KiB until the process exits.
+//
+// Host code must never pass the NAME of this array to a kernel — on the host the name is only a handle of the
+// runtime, not a device address.  static_argmax_scratch() asks the runtime for the real address, once per
+// device, with that device current.
+#define MVB200_STATIC_ARGMAX_KEYS (MVB200_GREEDY_ARGMAX_STATIC_BYTES / sizeof(unsigned long long))
+static __device__ __align__(256) unsigned long long g_static_argmax_partial[MVB200_STATIC_ARGMAX_KEYS];
+
+namespace mvb200 {
+
+constexpr int kMaxDevices = 64;
+static std::mutex g_static_argmax_mu;
+static unsigned long long* g_static_argmax_ptr[kMaxDevices];  // device address of the array, per device ordinal
+
+// Device address of g_static_argmax_partial on the CURRENT device (resolved on the first call per device).
+static int static_argmax_scratch(unsigned long long** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return fail(MVB200_ECUDA, "greedy_argmax_static: cudaGetDevice: %s", cudaGetErrorString(e));
+  if (dev < 0 || dev >= kMaxDevices)
+    return fail(MVB200_EUNSUPPORTED, "greedy_argmax_static: device ordinal %d beyond %d", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_static_argmax_mu);
+  if (!g_static_argmax_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_argmax_partial);
+    if (e != cudaSuccess || !p) {
+      (void)cudaGetLastError();
+      return fail(MVB200_ECUDA, "greedy_argmax_static: cudaGetSymbolAddress on device %d: %s", dev,
+                  cudaGetErrorString(e));
+    }
+    g_static_argmax_ptr[dev] = static_cast<unsigned long long*>(p);
+  }
+  *out = g_static_argmax_ptr[dev];
+  return MVB200_OK;
+}
+
+}  // namespace mvb200
+
+extern "C" int mvb200_greedy_argmax_static(const void* logits, int64_t row_stride, int32_t rows, int32_t vocab,
+                                           int32_t dtype, int64_t* out_index, float* out_value,
+                                           int64_t index_offset, void* stream) {
+  using namespace mvb200;
+  if (rows < 0 || vocab <= 0 || row_stride < vocab)
+    return fail(MVB200_EINVAL, "greedy_argmax_static: bad sizes (rows=%d vocab=%d stride=%lld)", rows, vocab,
+                (long long)row_stride);
+  if (rows == 0) return MVB200_OK;
+  if (!logits || !out_index) return fail(MVB200_EINVAL, "greedy_argmax_static: null pointer");
+  if (dtype != MVB200_BF16 && dtype != MVB200_F16 && dtype != MVB200_F32)
+    return fail(MVB200_EINVAL, "greedy_argmax_static: unknown dtype %d", dtype);
+  // a single chunk per row writes the result directly and touches no scratch at all
+  const size_t need = argmax_chunks(rows, vocab) > 1 ? mvb200_greedy_argmax_workspace_bytes(rows, vocab) : 0;
+  if (need > (size_t)MVB200_GREEDY_ARGMAX_STATIC_BYTES)
+    return fail(MVB200_EINVAL,
+                "greedy_argmax_static: rows=%d x vocab=%d needs %zu bytes of scratch, the built-in array holds %d; "
+                "use mvb200_greedy_argmax with a caller workspace", rows, vocab, need,
+                (int)MVB200_GREEDY_ARGMAX_STATIC_BYTES);
+  unsigned long long* scratch = nullptr;
+  if (int rc = static_argmax_scratch(&scratch)) return rc;
+  // Nothing to clear: pass one overwrites every key pass two reads (rows x chunks of them), so what an
+  // earlier call left behind is never seen.
+  cudaStream_t s = (cudaStream_t)stream;
+  note_kernel("greedy_argmax_static");
+  switch (dtype) {
+    case MVB200_BF16:
+      return launch_argmax<__nv_bfloat16>(logits, row_stride, rows, vocab, scratch, out_index, out_value, index_offset, s);
+    case MVB200_F16:
+      return launch_argmax<__half>(logits, row_stride, rows, vocab, scratch, out_index, out_value, index_offset, s);
+    default:
+      return launch_argmax<float>(logits, row_stride, rows, vocab, scratch, out_index, out_value, index_offset, s);
   }
 }
