@@ -36,6 +36,14 @@ struct SmemOptIn {
 };
 int optin_dynamic_smem(const void* kernel, int bytes, SmemOptIn* cache, const char* what);
 int device_sm_count();  // SMs of the current device (cached per device)
+// CTAs of `kernel` (threads, dynamic smem) the runtime says fit one SM at a time, per device (one static instance
+// per kernel).  Persistent kernels whose CTAs wait for each other size their grid from this, never from a guess.
+struct ResidentCtas {
+  int smem[64];
+  int ctas[64];
+};
+int resident_ctas_per_sm(const void* kernel, int threads, int smem_bytes, ResidentCtas* cache, const char* what,
+                         int* out);
 // A/B knobs (MVB200_DECODE_*, MVB200_ROPE_PAIR, ...) exist in the tuning build only (python minivllm_b200/build.py
 // --trace -> libmvb200_trace.so, selected with MVB200_LIB): the product library carries the measured defaults.
 inline const char* tuning_env(const char* name) {

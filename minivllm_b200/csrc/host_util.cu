@@ -73,6 +73,24 @@ int optin_dynamic_smem(const void* kernel, int bytes, SmemOptIn* cache, const ch
   return MVB200_OK;
 }
 
+int resident_ctas_per_sm(const void* kernel, int threads, int smem_bytes, ResidentCtas* cache, const char* what,
+                         int* out) {
+  const int d = current_device_slot();
+  if (cache->smem[d] != smem_bytes || cache->ctas[d] <= 0) {
+    int n = 0;
+    cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, (size_t)smem_bytes);
+    if (e != cudaSuccess)
+      return fail(MVB200_ECUDA, "%s: occupancy query failed on device %d: %s", what, d, cudaGetErrorString(e));
+    if (n < 1)
+      return fail(MVB200_EUNSUPPORTED, "%s: not one CTA (%d threads, %d B smem) fits an SM of device %d", what,
+                  threads, smem_bytes, d);
+    cache->smem[d] = smem_bytes;
+    cache->ctas[d] = n;
+  }
+  *out = cache->ctas[d];
+  return MVB200_OK;
+}
+
 bool pdl_enabled() {
   static const bool on = [] {
     const char* e = getenv("MVB200_NO_PDL");

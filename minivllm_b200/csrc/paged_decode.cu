@@ -156,6 +156,15 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
     pdl_launch_dependents();  // the next kernel may start its own prologue
   }
 
+  // Workspace stamp, checked by a consumer thread: it is past its dependency wait, so an init kernel launched just
+  // before this one on the stream (first decode after mvb200_decode_workspace_init) is complete and visible.  A
+  // run-ahead producer could read the stamp too early and trap on a workspace that is being initialised.
+  if (p.sched != nullptr && blockIdx.x == 0 && threadIdx.x == 0 &&
+      reinterpret_cast<volatile uint32_t*>(p.sched)[3] != kWorkspaceCookie) {
+    printf("mvb200: decode workspace was not initialised (mvb200_decode_workspace_init)\n");
+    __trap();
+  }
+
   T* out = reinterpret_cast<T*>(p.out);
 
   if (warp == kConsumerWarps) {
@@ -164,11 +173,6 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmap_k,
     // consumers' merge / write-out of one unit overlaps the loads of the next (no per-CTA prologue and
     // no wave tail as with one CTA per unit).  Ring entries of a unit: its n tiles, then one slot that
     // carries no data and is lent to the consumers as merge scratch.
-    if (p.sched != nullptr && blockIdx.x == 0 && lane == 0 &&
-        reinterpret_cast<volatile uint32_t*>(p.sched)[3] != kWorkspaceCookie) {
-      printf("mvb200: decode workspace was not initialised (mvb200_decode_workspace_init)\n");
-      __trap();
-    }
     int it = 0;
     bool waited = !run_ahead;  // false: nothing the preceding kernel writes may be touched yet
     // The first unit is the CTA's own index (no round trip to the counter before the first load); the next
@@ -833,9 +837,25 @@ static int launch_fast(DecodeParams& p, const void* k_cache, const void* v_cache
   static SmemOptIn optin;
   rc = optin_dynamic_smem((const void*)kern, smem, &optin, "paged_decode");
   if (rc) return rc;
-  // persistent grid: the CTAs that can be resident at once, or one per unit when there are fewer units
-  int64_t ctas = (int64_t)decode_ctas_per_sm() * device_sm_count();
+  // persistent grid: the CTAs that can be resident at once, or one per unit when there are fewer units.
+  // "Can be resident" is asked of the runtime, not assumed: the fused split reduction waits on tickets owed by
+  // other CTAs of the grid, so a CTA that is not co-resident with the waiters would never pay — a hang, not a
+  // slowdown.  More stages (tuning build), register growth or another carve-out lower the answer below
+  // decode_ctas_per_sm(); the grid follows it.
+  static ResidentCtas resident;  // per instantiation: (device, smem bytes) -> CTAs per SM
+  int per_sm = 0;
+  rc = resident_ctas_per_sm((const void*)kern, kDecodeThreads, smem, &resident, "paged_decode", &per_sm);
+  if (rc) return rc;
+  if (per_sm > decode_ctas_per_sm()) per_sm = decode_ctas_per_sm();
+  const int64_t capacity = (int64_t)per_sm * device_sm_count();
+  int64_t ctas = capacity;
   if (ctas > p.total_units) ctas = p.total_units;
+  // run-ahead pays where start-up latency shows: at most one unit per resident CTA (measured, run 7: with
+  // several units per CTA — 512 x 1024-token sequences on one kv head — it costs 7 us per launch)
+  if (p.total_units > capacity) p.early = 0;
+  // a run-ahead producer would queue the unit's Q copy behind the tiles it fetched early: the consumers (which wait
+  // for the preceding kernel at the top) read their Q fragments from global memory instead
+  if (p.early && tuning_env("MVB200_DECODE_EARLY_QBULK") == nullptr) p.q_bulk = 0;
   const bool fused = p.num_splits > 1 && decode_fused_reduce();
   if (p.num_splits > 1 && !fused) p.tickets = nullptr;
   // one unit per CTA: nothing to balance, skip the counter round trips
@@ -951,26 +971,8 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
                                       int32_t dtype, uint32_t flags, const mvb200_decode_store* store,
                                       void* stream) {
   using namespace mvb200;
-  if (store != nullptr && batch > 0 && k_cache && v_cache && num_blocks > 0) {
-    if (!store->key || !store->value || !store->slot_mapping)
-      return fail(MVB200_EINVAL, "paged_decode: fused store with a null pointer");
-    const int e = dtype == MVB200_F32 ? 4 : 2;
-    const bool fusable = e == 2 && (head_dim == 64 || head_dim == 128) && block_size % 64 == 0 && max_blocks_per_seq > 0 &&
-                         num_kv_heads > 0 && num_heads % num_kv_heads == 0 && num_heads / num_kv_heads <= 16 &&
-                         ((uintptr_t)store->key % 16 == 0) && ((uintptr_t)store->value % 16 == 0) &&
-                         store->key_row_stride % 8 == 0 && store->value_row_stride % 8 == 0 &&
-                         ((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) && ((uintptr_t)q % 4 == 0) &&
-                         (q_row_stride % 2 == 0) && num_blocks < (1LL << 31) && tuning_env("MVB200_DECODE_NO_FUSED_STORE") == nullptr;
-    if (!fusable) {
-      const int rc = mvb200_store_kvcache(store->key, store->value, store->key_row_stride, store->value_row_stride,
-                                          (void*)k_cache, (void*)v_cache, store->slot_mapping, batch,
-                                          num_kv_heads * head_dim, num_blocks * (int64_t)block_size, dtype, stream);
-      if (rc) return rc;
-      store = nullptr;
-    }
-  } else {
-    store = nullptr;
-  }
+  // Every argument check comes before the first write: a call that returns an error has not touched the cache
+  // (the separate-launch path, store_kv_cache then attention, fails the same way: attention.py:237-243).
   if (batch < 0 || num_heads <= 0 || num_kv_heads <= 0 || head_dim <= 0 || block_size <= 0)
     return fail(MVB200_EINVAL, "paged_decode: bad sizes");
   if (num_heads % num_kv_heads)
@@ -981,7 +983,37 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
   cudaStream_t s = (cudaStream_t)stream;
   const int eb = dtype == MVB200_F32 ? 4 : ((dtype == MVB200_F16 || dtype == MVB200_BF16) ? 2 : 0);
   if (!eb) return fail(MVB200_EINVAL, "paged_decode: unknown dtype %d", dtype);
-  if (max_blocks_per_seq <= 0 || num_blocks <= 0) {
+  const bool zero_width = max_blocks_per_seq <= 0 || num_blocks <= 0;
+  if (!zero_width && (!k_cache || !v_cache || !block_tables))
+    return fail(MVB200_EINVAL, "paged_decode: null cache or block table");
+  if (store != nullptr && k_cache && v_cache && num_blocks > 0 &&
+      (!store->key || !store->value || !store->slot_mapping))
+    return fail(MVB200_EINVAL, "paged_decode: fused store with a null pointer");
+  const int group = num_heads / num_kv_heads;
+  const bool fast = !zero_width && eb == 2 && (head_dim == 64 || head_dim == 128) && block_size % 64 == 0 &&
+                    group <= 16 && num_blocks < (1LL << 31) &&
+                    ((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) &&
+                    ((uintptr_t)q % 4 == 0) && (q_row_stride % 2 == 0);
+  if (!zero_width && !fast) {
+    if (head_dim > 256) return fail(MVB200_EUNSUPPORTED, "paged_decode: head_dim %d > 256", head_dim);
+    if (batch > 65535) return fail(MVB200_EUNSUPPORTED, "paged_decode: batch %d > 65535", batch);
+  }
+  if (store != nullptr && k_cache && v_cache && num_blocks > 0) {
+    const bool fusable = fast && max_blocks_per_seq > 0 &&
+                         ((uintptr_t)store->key % 16 == 0) && ((uintptr_t)store->value % 16 == 0) &&
+                         store->key_row_stride % 8 == 0 && store->value_row_stride % 8 == 0 &&
+                         tuning_env("MVB200_DECODE_NO_FUSED_STORE") == nullptr;
+    if (!fusable) {
+      const int rc = mvb200_store_kvcache(store->key, store->value, store->key_row_stride, store->value_row_stride,
+                                          (void*)k_cache, (void*)v_cache, store->slot_mapping, batch,
+                                          num_kv_heads * head_dim, num_blocks * (int64_t)block_size, dtype, stream);
+      if (rc) return rc;
+      store = nullptr;
+    }
+  } else {
+    store = nullptr;
+  }
+  if (zero_width) {
     // zero-width block table (engine warm-up): zeros, like page_attention.py:62-65
     for (int b = 0; b < batch; ++b) {
       cudaError_t e = cudaMemsetAsync((char*)out + (int64_t)b * out_row_stride * eb, 0,
@@ -991,14 +1023,7 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
     note_kernel("decode_zero");
     return MVB200_OK;
   }
-  if (!k_cache || !v_cache || !block_tables)
-    return fail(MVB200_EINVAL, "paged_decode: null cache or block table");
   if (num_splits < 1) num_splits = 1;
-  const int group = num_heads / num_kv_heads;
-  const bool fast = eb == 2 && (head_dim == 64 || head_dim == 128) && block_size % 64 == 0 &&
-                    group <= 16 && num_blocks < (1LL << 31) &&
-                    ((uintptr_t)k_cache % 16 == 0) && ((uintptr_t)v_cache % 16 == 0) &&
-                    ((uintptr_t)q % 4 == 0) && (q_row_stride % 2 == 0);
   if (fast) {
     DecodeParams p;
     p.q = q;
@@ -1045,15 +1070,11 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
     p.total_units = (int32_t)(units * num_splits);
     p.q_bulk = (((uintptr_t)q & 15) == 0 && (q_row_stride % 8) == 0) ? 1 : 0;
     static const bool no_early = tuning_env("MVB200_DECODE_NO_EARLY") != nullptr;
-    // run-ahead pays where start-up latency shows: at most one unit per resident CTA (measured, run 7: with
-    // several units per CTA — 512 x 1024-token sequences on one kv head — it costs 7 us per launch)
-    // The fused store does not stand in the way: the new rows are read by a CONSUMER warp, after its own dependency
-    // wait (runs 31/32: one-launch step of the small shapes -7 ... -11 %).
-    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early &&
-               p.total_units <= (int64_t)decode_ctas_per_sm() * device_sm_count()) ? 1 : 0;
-    // a run-ahead producer would queue the unit's Q copy behind the tiles it fetched early: the consumers (which wait
-    // for the preceding kernel at the top) read their Q fragments from global memory instead
-    if (p.early && tuning_env("MVB200_DECODE_EARLY_QBULK") == nullptr) p.q_bulk = 0;
+    // Run-ahead is requested here and confirmed in launch_fast, which knows how many CTAs are resident (it is
+    // kept only with at most one unit per resident CTA).  The fused store does not stand in the way: the new rows
+    // are read by a CONSUMER warp, after its own dependency wait (runs 31/32: one-launch step of the small
+    // shapes -7 ... -11 %).
+    p.early = ((flags & MVB200_DECODE_KV_PREFIX_STABLE) && pdl_enabled() && !no_early) ? 1 : 0;
     p.new_k = store ? store->key : nullptr;
     p.new_v = store ? store->value : nullptr;
     p.new_k_stride = store ? store->key_row_stride : 0;
@@ -1077,9 +1098,6 @@ extern "C" int mvb200_paged_decode_ex(const void* q, int64_t q_row_stride, const
                                         num_kv_heads * head_dim, num_blocks * (int64_t)block_size, dtype, stream);
     if (rc) return rc;
   }
-  if (head_dim > 256)
-    return fail(MVB200_EUNSUPPORTED, "paged_decode: head_dim %d > 256", head_dim);
-  if (batch > 65535) return fail(MVB200_EUNSUPPORTED, "paged_decode: batch %d > 65535", batch);
   note_kernel("decode_generic");
   switch (dtype) {
     case MVB200_F32:

@@ -453,6 +453,38 @@ def test_decode_with_fused_store(m, cuda_device, dtype, batch, kvh, g, d, splits
         m.paged_decode_attention(q, k2, v2, bt, cl, d**-0.5, new_key=k, new_value=v, slot_mapping=slots[:-1])
 
 
+def test_decode_error_leaves_the_cache_untouched(m, cuda_device):
+    """A ``mvb200_paged_decode_ex`` call that is refused must not have stored the step's tokens first:
+    head_dim 320 has no kernel (EUNSUPPORTED) and its store is not fusable, so the separate store launch used to
+    run before the refusal.  Called through the C ABI; ``ops`` would stop the shape earlier."""
+    import ctypes
+
+    native = m._native
+    b, kvh, h, d, bs, nb = 2, 2, 4, 320, 64, 4
+    kc = torch.randn(nb, bs, kvh, d, device=cuda_device)
+    vc = torch.randn(nb, bs, kvh, d, device=cuda_device)
+    k0, v0 = kc.clone(), vc.clone()
+    q = torch.randn(b, h, d, device=cuda_device)
+    out = torch.zeros_like(q)
+    k = torch.randn(b, kvh, d, device=cuda_device)
+    v = torch.randn(b, kvh, d, device=cuda_device)
+    bt = torch.tensor([[0, 1], [2, 3]], dtype=torch.int32, device=cuda_device)
+    cl = torch.tensor([5, 70], dtype=torch.int32, device=cuda_device)
+    slots = torch.tensor([4, 3 * bs + 5], dtype=torch.int32, device=cuda_device)
+    store = native.DecodeStore(k.data_ptr(), v.data_ptr(), kvh * d, kvh * d, slots.data_ptr())
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+    def call(head_dim, dtype_code):
+        return native.lib().mvb200_paged_decode_ex(
+            q.data_ptr(), h * d, kc.data_ptr(), vc.data_ptr(), bt.data_ptr(), 2, cl.data_ptr(), out.data_ptr(), h * d,
+            None, 0, b, h, kvh, head_dim, bs, nb, 2, 1, d**-0.5, dtype_code, 0, ctypes.byref(store), stream)
+
+    assert call(d, 0) == 2 and "head_dim" in native.last_error()
+    assert call(d, 7) == 1 and "dtype" in native.last_error()
+    torch.cuda.synchronize()
+    assert torch.equal(kc, k0) and torch.equal(vc, v0)
+
+
 # ---------------------------------------------------------------------------
 # prefill
 # ---------------------------------------------------------------------------
