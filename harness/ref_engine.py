@@ -183,6 +183,10 @@ def run(
 
         info["last_kernel"] = minivllm_b200.ops.last_kernel()
         info["kernels_seen"] = sorted(minivllm_b200.ops.kernels_seen())
+        if peer_allreduce:
+            from minivllm_b200 import reference_patch
+
+            info["allreduce"] = reference_patch.peer_allreduce_status()
     ex = llm.model_runner.inference_executor
     info["graphs_captured"] = sorted(getattr(ex, "graphs", {}).keys())
     info["kv_heads_per_rank"] = int(ex.kv_cache.size(4)) if ex.kv_cache is not None else None

@@ -18,6 +18,10 @@ from . import _native
 from .ops import _code, _require_cuda, _stream
 
 
+class PeerSetupError(RuntimeError):
+    """Raised on EVERY rank of the group when the peer mapping could not be set up on at least one of them."""
+
+
 class PeerAllReduce:
     """Per-rank endpoint.  Build one per process with ``PeerAllReduce(rank, world, max_bytes, group=...)``
     (handles travel through ``all_gather_object``) or ``PeerAllReduce.local_group`` for ``world`` endpoints
@@ -34,26 +38,51 @@ class PeerAllReduce:
         self.slot_bytes = (int(max_bytes) + 255) // 256 * 256
         self._lib = lib
         self._opened: list[int] = []
-        with torch.cuda.device(self.device):
-            self._data = self._alloc(2 * (world + 2) * self.slot_bytes)
-            self._flags = self._alloc(lib.mvb200_peer_flag_bytes())
-            self._epoch = self._alloc(lib.mvb200_peer_epoch_bytes())
+        self._data = self._flags = self._epoch = None
         self.data_ptrs = (ctypes.c_void_p * 8)()
         self.flag_ptrs = (ctypes.c_void_p * 8)()
-        self.data_ptrs[rank], self.flag_ptrs[rank] = self._data, self._flags
-        if _defer:
+        if _defer or world == 1:
+            self._alloc_own()
             return
-        if world > 1:
-            import torch.distributed as dist
+        # Several processes: success must be agreed on.  A rank that fails alone (no P2P to one peer, IPC limits,
+        # out of memory) must still take part in every collective below, or its peers wait for it forever; and the
+        # peers must learn of it, or they would spin in the kernel's flag wait while it has gone back to NCCL.
+        # So: nothing that can fail sits between the collectives unguarded, and the outcome is all-gathered.
+        import torch.distributed as dist
 
+        error: Exception | None = None
+        mine = None
+        try:
+            self._alloc_own()
             mine = (self._export(self._data), self._export(self._flags))
-            everyone: list = [None] * world
-            dist.all_gather_object(everyone, mine, group=group)
-            with torch.cuda.device(self.device):
-                for r, (hd, hf) in enumerate(everyone):
-                    if r != rank:
-                        self.data_ptrs[r], self.flag_ptrs[r] = self._open(hd), self._open(hf)
-            dist.barrier(group=group)
+        except Exception as e:  # noqa: BLE001  reported collectively below
+            error = e
+        everyone: list = [None] * world
+        dist.all_gather_object(everyone, mine, group=group)
+        if error is None and all(h is not None for h in everyone):
+            try:
+                with torch.cuda.device(self.device):
+                    for r, (hd, hf) in enumerate(everyone):
+                        if r != rank:
+                            self.data_ptrs[r], self.flag_ptrs[r] = self._open(hd), self._open(hf)
+            except Exception as e:  # noqa: BLE001
+                error = e
+        # doubles as the barrier: nobody launches before every rank has mapped every peer
+        outcome: list = [None] * world
+        dist.all_gather_object(outcome, None if error is None else f"{type(error).__name__}: {error}", group=group)
+        bad = {r: msg for r, msg in enumerate(outcome) if msg is not None}
+        if bad:
+            self.close()
+            raise PeerSetupError(f"peer all-reduce unavailable, set-up failed on rank(s) {sorted(bad)}: "
+                                 + "; ".join(f"[{r}] {m}" for r, m in sorted(bad.items())))
+
+    def _alloc_own(self) -> None:
+        lib = self._lib
+        with torch.cuda.device(self.device):
+            self._data = self._alloc(2 * (self.world + 2) * self.slot_bytes)
+            self._flags = self._alloc(lib.mvb200_peer_flag_bytes())
+            self._epoch = self._alloc(lib.mvb200_peer_epoch_bytes())
+        self.data_ptrs[self.rank], self.flag_ptrs[self.rank] = self._data, self._flags
 
     # ---- construction helpers -------------------------------------------------------------------
     @classmethod

@@ -230,13 +230,32 @@ def _peer_comm(device: torch.device):
 
         from .comm import PeerAllReduce
 
+        from .comm import PeerSetupError
+
+        gloo = dist.new_group(backend="gloo")  # handle exchange only; a collective every rank makes
         try:
-            gloo = dist.new_group(backend="gloo")  # handle exchange only
+            # The constructor agrees on the outcome across the group: it either succeeds on every rank or raises
+            # PeerSetupError on every rank (e.g. no peer access between one pair of devices), so all ranks take the
+            # same branch here and nobody is left waiting in a barrier or in the kernel for a rank that fell back.
             comm = PeerAllReduce(dist.get_rank(), dist.get_world_size(), PEER_ALLREDUCE_MAX_BYTES, group=gloo, device=device)
             _PEER_COMM["comm"] = comm
-        except Exception:  # noqa: BLE001  (no peer access between the ranks' devices: stay on NCCL)
-            _PEER_COMM["failed"] = True
+        except PeerSetupError as e:  # stay on NCCL, on all ranks
+            _PEER_COMM["failed"] = str(e)
     return comm
+
+
+def peer_allreduce_status() -> dict:
+    """Which collective served the row-parallel all-reduces of this process so far (calls made from Python: a call
+    captured into a CUDA graph counts once, at capture).  ``collective`` is ``"mvb200_peer_one_shot"`` when the peer
+    kernel is in use, ``"nccl"`` when the set-up failed on some rank (``failed`` says why) or was never installed."""
+    comm = _PEER_COMM.get("comm")
+    return {
+        "installed": bool(_PEER_COMM.get("installed")),
+        "collective": "mvb200_peer_one_shot" if comm is not None else "nccl",
+        "failed": _PEER_COMM.get("failed") or None,
+        "peer_calls": int(_PEER_COMM.get("peer_calls", 0)),
+        "nccl_calls": int(_PEER_COMM.get("nccl_calls", 0)),
+    }
 
 
 #: messages up to this size (decode steps: max_num_seqs x hidden elements) take the one-shot peer kernel, larger
@@ -263,12 +282,15 @@ def install_peer_allreduce() -> None:
             if y.is_cuda and y.dim() == 2 and y.is_contiguous() and y.numel() * y.element_size() <= PEER_ALLREDUCE_MAX_BYTES:
                 comm = _peer_comm(y.device)
                 if comm is not None and comm.fits(y):
+                    _PEER_COMM["peer_calls"] = _PEER_COMM.get("peer_calls", 0) + 1
                     return comm.all_reduce(y, algo=1)
+            _PEER_COMM["nccl_calls"] = _PEER_COMM.get("nccl_calls", 0) + 1
             dist.all_reduce(y)
         return y
 
     cls.forward = forward
     cls._mvb200_peer = True
+    _PEER_COMM["installed"] = True
 
 
 def hot_graph_sizes(max_batch_size: int) -> list[int]:

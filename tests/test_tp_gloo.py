@@ -156,3 +156,51 @@ def test_reference_engine_tp2_gloo_matches_its_single_rank_stream():
         assert ret["worker"] is True
         assert ret["kv_heads_rank0"] == 1  # tiny-qwen3 has 2 KV heads: one per rank in the cache
         assert ret["tokens"] == want
+
+
+def _peer_setup_worker(rank: int, world: int, port: int, fail_rank: int, fail_at: str, ret):
+    """PeerAllReduce set-up with one rank failing alone (device calls stubbed: no GPU here)."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import contextlib
+
+        from minivllm_b200 import comm
+
+        closed = []
+        comm.PeerAllReduce._alloc = lambda self, n: (_ for _ in ()).throw(RuntimeError("out of memory")) \
+            if (fail_at == "alloc" and rank == fail_rank) else 0x1000 * (rank + 1)
+        comm.PeerAllReduce._export = lambda self, ptr: bytes([rank]) * 64
+        comm.PeerAllReduce._open = lambda self, h: (_ for _ in ()).throw(RuntimeError("peer access unsupported")) \
+            if (fail_at == "open" and rank == fail_rank) else 0x9000
+        comm.PeerAllReduce.close = lambda self: closed.append(rank)
+        comm.torch.cuda.device = lambda d: contextlib.nullcontext()
+        try:
+            comm.PeerAllReduce(rank, world, 4096, device="cpu")
+            ret[rank] = "ok"
+        except comm.PeerSetupError as e:
+            ret[rank] = f"{e}|closed={closed}"
+        dist.barrier()  # every rank got here: nobody is stuck in the set-up
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("fail_at", ["alloc", "open", "none"])
+def test_peer_allreduce_setup_outcome_is_collective(fail_at):
+    """a rank whose IPC open (or allocation) fails alone must not fall back to NCCL by itself while
+    its peers wait for it — every rank raises PeerSetupError (and closes its endpoint) or every rank succeeds."""
+    ctx = mp.get_context("spawn")
+    with ctx.Manager() as mgr:
+        ret = mgr.dict()
+        port = _free_port()
+        procs = [ctx.Process(target=_peer_setup_worker, args=(r, 2, port, 1, fail_at, ret)) for r in range(2)]
+        for p in procs:
+            p.start()
+        for p in procs:
+            p.join(120)
+        assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+        if fail_at == "none":
+            assert ret[0] == ret[1] == "ok"
+        else:
+            for r in range(2):
+                assert "rank(s) [1]" in ret[r] and f"closed=[{r}]" in ret[r], ret[r]
