@@ -120,8 +120,9 @@ MVB200_API int mvb200_paged_decode(const void* q, int64_t q_row_stride,
 /* The caller vouches that the kernel launched immediately before this one on the stream writes neither
  * block_tables / context_lens nor any K/V row other than the NEWEST token of each sequence (position
  * context_lens[b] - 1) — true for the layer's decode path, whose predecessor is the store_kvcache of the
- * step's new tokens (attention.py:237-243).  Under programmatic dependent launch the kernel then starts
- * streaming the older K/V tiles while that predecessor is still draining. */
+ * step's new tokens (attention.py:237-243).  Under programmatic dependent launch the kernel then reads the
+ * metadata and starts streaming the older K/V tiles while that predecessor is still draining — so context_lens
+ * and block_tables must be final BEFORE the predecessor starts, not merely before this call. */
 #define MVB200_DECODE_KV_PREFIX_STABLE 1u
 
 /* The step's new tokens, to be stored by the decode kernel itself (fused store_kvcache, saves one launch per

@@ -116,6 +116,11 @@ class Attention(nn.Module):
             q, k, v = q.to(k_cache.dtype), k.to(k_cache.dtype), v.to(k_cache.dtype)
 
         fuse_store = None
+        # True only while the launch that precedes the decode kernel on the stream is known to write nothing the
+        # run-ahead producer reads before its dependency wait (context_lens, block_tables, every K/V row but the
+        # newest): the fused q/k path's own store (stored=True), our decode-shaped store_kvcache below, or — with the
+        # store fused into the decode kernel — the caller's projection / rotary kernels, which produce q, k, v only.
+        predecessor_known = stored
         if has_cache:
             self._cache_initialized = True
             slots = context.slot_mapping
@@ -124,8 +129,13 @@ class Attention(nn.Module):
                         and context.block_tables.dim() == 2 and context.block_tables.size(1) > 0
                         and slots.numel() == q.size(0) and k.dim() == 3):
                     fuse_store = (k, v, slots)  # decode: the attention kernel stores the new token itself
+                    predecessor_known = True
                 else:
                     ops.store_kvcache(k, v, k_cache, v_cache, slots)
+                    # one slot per sequence = the step's newest positions (inference_executor.py:568-572); any
+                    # other slot shape may rewrite older rows, which a run-ahead producer could read stale
+                    predecessor_known = (not context.is_prefill and context.context_lens is not None
+                                         and slots.numel() == context.context_lens.numel())
         elif not context.is_prefill and not self._cache_initialized:
             raise RuntimeError(
                 "KV cache has not been initialized. Ensure ModelRunner.allocate_kv_cache() "
@@ -162,9 +172,9 @@ class Attention(nn.Module):
             q, k_cache, v_cache, context.block_tables, context.context_lens, self.scale,
             num_splits=getattr(context, "decode_num_splits", None),
             workspace=getattr(context, "decode_workspace", None),
-            # the launch before this one is the store of the step's new tokens (one slot per sequence, the
-            # newest position: inference_executor.py:568-572) or nothing of ours at all
-            kv_prefix_stable=True,
+            # run-ahead only behind a predecessor we know (see above); the executor uploads the step's metadata
+            # before the model runs, so no launch between it and this one writes context_lens / block_tables
+            kv_prefix_stable=predecessor_known,
             **({"new_key": fuse_store[0], "new_value": fuse_store[1], "slot_mapping": fuse_store[2]} if fuse_store else {}),
         )
 

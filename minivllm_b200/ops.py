@@ -17,6 +17,7 @@ Reference call sites (relative to the reference repository):
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -245,6 +246,26 @@ def _default_decode_workspace(need: int, device: torch.device) -> torch.Tensor:
     return ws
 
 
+_DEBUG_CHECKS = os.environ.get("MVB200_DEBUG_CHECKS", "") not in ("", "0")
+
+
+def _check_decode_slots(slot_mapping: torch.Tensor, block_tables: torch.Tensor, context_lens: torch.Tensor,
+                        block_size: int) -> None:
+    """The fused store's contract (include/mvb200.h, ``mvb200_decode_store``): row ``b`` goes to the slot of position
+    ``context_lens[b] - 1`` of sequence ``b``.  A slot elsewhere would be patched into the wrong smem row and the
+    attention output would differ from the cache.  Padding rows (slot < 0 or context <= 0) are exempt."""
+    pos = context_lens.long() - 1
+    live = (slot_mapping >= 0) & (pos >= 0)
+    col = (pos.clamp(min=0) // block_size).clamp(max=block_tables.size(1) - 1)
+    want_block = block_tables.gather(1, col.unsqueeze(1)).squeeze(1).long()
+    ok = (slot_mapping.long() // block_size == want_block) & (slot_mapping.long() % block_size == pos % block_size)
+    bad = (live & ~ok).nonzero().flatten()
+    if bad.numel():
+        b = int(bad[0])
+        raise ValueError(f"paged_decode: slot_mapping[{b}] = {int(slot_mapping[b])} is not the slot of position "
+                         f"context_lens[{b}] - 1 = {int(pos[b])} (block {int(want_block[b])}, block_size {block_size})")
+
+
 def paged_decode_attention(
     q: torch.Tensor,
     k_cache: torch.Tensor,
@@ -264,8 +285,13 @@ def paged_decode_attention(
     """``softmax(scale * q K^T) V`` of one query token per sequence over paged KV.
 
     ``kv_prefix_stable=True`` (``MVB200_DECODE_KV_PREFIX_STABLE``): the kernel launched just before this call
-    writes nothing but the newest token of each sequence (and q) — the kernel may then fetch older K/V tiles
-    before that predecessor has finished (programmatic dependent launch).
+    writes nothing but the newest token of each sequence (and q) — in particular neither ``context_lens`` nor
+    ``block_tables``, which must be in place before that predecessor starts.  The kernel may then read the
+    metadata and fetch older K/V tiles before the predecessor has finished (programmatic dependent launch).
+    Leave it off when a metadata update or a store of older rows directly precedes the call.
+
+    ``MVB200_DEBUG_CHECKS=1`` in the environment makes a call with a fused store verify (host sync, not
+    capturable) that ``slot_mapping[b] // block_size == block_tables[b, (context_lens[b]-1) // block_size]``.
 
     ``new_key`` / ``new_value`` ``[B, KVH, D]`` + ``slot_mapping [B]``: the step's new tokens, stored into the
     caches by the decode kernel itself (``store_kvcache`` fused in: bit-identical cache contents, one launch
@@ -339,6 +365,8 @@ def paged_decode_attention(
             raise ValueError(f"slot_mapping size ({slot_mapping.numel()}) must match number of tokens ({b})")
         if not slot_mapping.is_contiguous():
             slot_mapping = slot_mapping.contiguous()
+        if _DEBUG_CHECKS and mb > 0 and not torch.cuda.is_current_stream_capturing():
+            _check_decode_slots(slot_mapping, block_tables, context_lens, bs)
         store = _native.DecodeStore(new_key.data_ptr(), new_value.data_ptr(), _row_stride(new_key), _row_stride(new_value),
                                     slot_mapping.data_ptr())
     rc = _native.lib().mvb200_paged_decode_ex(

@@ -158,3 +158,20 @@ def test_dropin_surface_against_reference(tmp_path):
     assert proc.returncode == 0, proc.stdout[-2000:] + "\n" + proc.stderr[-4000:]
     assert "QWEN_BLOCK_OK" in proc.stdout
     assert "DROPIN_OK" in proc.stdout
+
+
+def test_debug_check_of_the_fused_store_slots():
+    """``ops._check_decode_slots`` (MVB200_DEBUG_CHECKS=1): slot b must be the slot of position context_lens[b]-1
+    (inference_executor.py:568-572); padding rows are exempt.  Pure tensor logic, runs on CPU."""
+    import torch
+
+    from minivllm_b200 import ops
+
+    bt = torch.tensor([[3, 5, -1], [7, -1, -1], [2, 4, 6]], dtype=torch.int32)
+    cl = torch.tensor([70, 1, 0], dtype=torch.int32)
+    good = torch.tensor([5 * 64 + 5, 7 * 64, -1], dtype=torch.int32)
+    ops._check_decode_slots(good, bt, cl, 64)
+    with pytest.raises(ValueError, match=r"slot_mapping\[0\]"):
+        ops._check_decode_slots(torch.tensor([3 * 64 + 5, 7 * 64, -1], dtype=torch.int32), bt, cl, 64)
+    with pytest.raises(ValueError, match=r"slot_mapping\[1\]"):
+        ops._check_decode_slots(torch.tensor([5 * 64 + 5, 7 * 64 + 1, -1], dtype=torch.int32), bt, cl, 64)
