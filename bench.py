@@ -290,20 +290,24 @@ def load_peaks():
         return {}
 
 
-def matching_traffic(wl_key, kvh_rank, batch, ctx_sum):
+def matching_traffic(wl_key, kvh_rank, batch, ctx_sum, q_heads_rank=None):
     """``roofline.traffic``: the ncu ``dram__bytes_read + dram__bytes_write`` per launch — only when a capture of
-    exactly this workload and per-rank shape is on file (profiles/decode_traffic.json), else None."""
+    exactly this PER-RANK launch shape is on file (profiles/decode_traffic.json), else None.  The workload name is not
+    part of the match: one rank of ``--gpus 8 --workload cfg2`` launches the shape captured as ``cfg2tp8`` (verdict
+    r2, 5c); ``wl_key`` only breaks ties between captures of the same shape."""
     try:
         rows = json.load(open(os.path.join(ROOT, "profiles", "decode_traffic.json")))
     except Exception:
         return None
     rows = rows if isinstance(rows, list) else [rows]
+    hits = []
     for r in rows:
         shape = r.get("shape", {})
         if shape.get("kv_heads_per_rank") == kvh_rank and shape.get("batch") == batch and shape.get("ctx_sum") == ctx_sum \
-                and r.get("workload_key") == wl_key:
-            return r.get("dram_bytes_per_launch")
-    return None
+                and (q_heads_rank is None or shape.get("q_heads_per_rank") in (None, q_heads_rank)):
+            hits.append(r)
+    hits.sort(key=lambda r: r.get("workload_key") != wl_key)
+    return hits[0].get("dram_bytes_per_launch") if hits else None
 
 
 # ---------------------------------------------------------------------------
@@ -547,7 +551,7 @@ def run_decode(env: Env, args, wl, wl_key) -> dict:
         "tokens_per_s_attention_only": B / (ms_step * 1e-3),
         "roofline": {
             "bound": "hbm", "kernel": "paged_decode_kernel<bf16,128>", "achieved": achieved, "peak": peak,
-            "unit": "GB/s", "frac": achieved / peak, "traffic": matching_traffic(wl_key, KVH, B, ctx_sum),
+            "unit": "GB/s", "frac": achieved / peak, "traffic": matching_traffic(wl_key, KVH, B, ctx_sum, H),
             "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy, read+write)" if peaks else "fallback 6650 GB/s",
             "frac_of_8TBps_spec": achieved / 8000.0,
             "bytes_per_launch": bytes_layer_rank, "us_per_launch": ms_dec / L * 1e3,
@@ -821,6 +825,8 @@ def run_engine(env: Env | None, args, wl) -> dict:
         "prefix_cache_hit_blocks": c["cache_hits"], "graphs_captured": info["graphs_captured"],
         "attention_classes": info["attention_classes"], "kernels_seen": info.get("kernels_seen"),
         "engine_init_s": info["init_s"],
+        # which collective served the row-parallel all-reduces (None at TP 1: there are none)
+        "allreduce": info.get("allreduce"),
     }
 
 

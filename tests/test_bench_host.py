@@ -34,7 +34,12 @@ def test_traffic_is_reported_only_for_the_captured_shape():
     r = rows[0]
     sh = r["shape"]
     assert bench.matching_traffic(r["workload_key"], sh["kv_heads_per_rank"], sh["batch"], sh["ctx_sum"]) == r["dram_bytes_per_launch"]
-    assert bench.matching_traffic(r["workload_key"], 1, sh["batch"], sh["ctx_sum"]) is None       # TP8 rank shape
+    # one rank of `--gpus 8 --workload cfg2` launches the shape captured as cfg2tp8: matched by shape, not by name
+    tp8 = [x for x in rows if x["workload_key"] == "cfg2tp8"]
+    if tp8:
+        assert bench.matching_traffic("cfg2", 1, 256, 524288, 2) == tp8[0]["dram_bytes_per_launch"]
+    assert bench.matching_traffic(r["workload_key"], 3, sh["batch"], sh["ctx_sum"]) is None     # a shape never captured
+    assert bench.matching_traffic(r["workload_key"], sh["kv_heads_per_rank"], sh["batch"], sh["ctx_sum"], 999) is None
     assert bench.matching_traffic("cfg4", 4, 1, 32768) is None or any(x["workload_key"] == "cfg4" for x in rows)
 
 
