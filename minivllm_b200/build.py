@@ -21,8 +21,8 @@ SOURCES = [
     "prefill_dbs.cu",
     "prefill_api.cu",
 ]
-# tuning build only (--trace): the first-generation prefill kernel and the knob matrix of the 2q kernel
-TUNING_SOURCES = ["prefill_tcgen05.cu"]
+# tuning build only (--trace): the first-generation prefill kernel, kept under probes/ (not product code) for A/B runs
+TUNING_SOURCES = [os.path.join(os.path.dirname(HERE), "probes", "prefill_tcgen05.cu")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
@@ -68,9 +68,9 @@ def _build(LIB: str, objdir: str, extra: list, verbose: bool, sources: list) -> 
     procs = []
     objs = []
     for src in sources:
-        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        obj = os.path.join(objdir, os.path.basename(src).replace(".cu", ".o"))
         objs.append(obj)
-        cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *extra, "-I", CSRC, "-c", os.path.join(CSRC, src), "-o", obj]  # join keeps absolute paths
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
