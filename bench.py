@@ -310,6 +310,21 @@ def matching_traffic(wl_key, kvh_rank, batch, ctx_sum, q_heads_rank=None):
     return hits[0].get("dram_bytes_per_launch") if hits else None
 
 
+def matching_prefill_traffic(seqs, cached, new, q_heads_rank, kvh_rank, head_dim):
+    """The prefill leg's ``roofline.traffic``: ncu DRAM bytes per launch of the prefill kernel when a capture of
+    exactly this per-rank shape is on file (profiles/prefill_traffic.json), else None."""
+    try:
+        rows = json.load(open(os.path.join(ROOT, "profiles", "prefill_traffic.json")))
+    except Exception:
+        return None
+    want = {"sequences": seqs, "cached_tokens": cached, "new_tokens": new, "q_heads_per_rank": q_heads_rank,
+            "kv_heads_per_rank": kvh_rank, "head_dim": head_dim}
+    for r in rows if isinstance(rows, list) else [rows]:
+        if r.get("shape") == want:
+            return r.get("dram_bytes_per_launch")
+    return None
+
+
 # ---------------------------------------------------------------------------
 # reference arm / cpu_baseline: the reference's own CPU eager path on a bounded sample
 # ---------------------------------------------------------------------------
@@ -708,7 +723,7 @@ def run_prefill(env: Env, args, wl, steps=None) -> dict:
                    "parallelism": f"tp{tp}", "cuda_graph": False, "l2": "192 MB write between timed steps flushes the 126 MB L2"},
         "tokens_per_s_attention_only": N / (ms_step * 1e-3),
         "roofline": {"bound": "tensor", "kernel": kernel, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak, "traffic": matching_prefill_traffic(S, C, NQ, H, KVH, D),
                      "peak_source": "MEASURED_PEAKS.json bf16_tflops_sustained (kernel timed inside a 36-layer step)" if peaks else "fallback 1400 TFLOP/s",
                      "frac_of_burst_peak": achieved / float(peaks.get("bf16_tflops", 1590.0)),
                      "flops_per_launch": fl_layer, "us_per_launch": ms_attn / L * 1e3},

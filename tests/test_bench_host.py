@@ -43,6 +43,13 @@ def test_traffic_is_reported_only_for_the_captured_shape():
     assert bench.matching_traffic("cfg4", 4, 1, 32768) is None or any(x["workload_key"] == "cfg4" for x in rows)
 
 
+def test_prefill_traffic_is_matched_on_the_captured_shape():
+    wl = bench.WORKLOADS["cfg3p"]
+    t = bench.matching_prefill_traffic(wl["seqs"], wl["cached"], wl["new"], wl["H"], wl["KVH"], wl["D"])
+    assert t is not None and 1.0 < t / (8 * 1024 * 32 * 128 * 2 * 2 + 8 * 2048 * 8 * 128 * 2 * 2) < 2.0  # 1.5x algorithmic (K/V re-streamed per head)
+    assert bench.matching_prefill_traffic(wl["seqs"], wl["cached"], wl["new"], wl["H"] // 2, wl["KVH"] // 2, wl["D"]) is None
+
+
 def test_engine_prompts_share_the_cached_prefix():
     wl = bench.WORKLOADS["cfg3e"]
     warm, real = bench.engine_prompts(wl, 151936)
